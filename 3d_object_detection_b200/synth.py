@@ -1,0 +1,122 @@
+"""Seeded synthetic LiDAR frames (S1 clustered, S2 ring, S3 uniform box, S4 edge set).
+
+All generators return C-contiguous float32 ``(N, 4)`` arrays ``[x, y, z, intensity]`` built from
+``numpy.random.default_rng(seed)``; there is no dataset on the box (BASELINE.json: synthetic frames).
+"""
+from __future__ import annotations
+
+import numpy as np
+
+from .config import GridGeometry
+
+# occupied-cell targets for S1 per grid key
+S1_CELLS = {"20cm": 12000, "10cm": 15000, "nuscene": 9000, "16cm": 12000}
+
+
+def frame_seed(config_id: int, frame_id: int) -> int:
+    return 1000 * int(config_id) + int(frame_id)
+
+
+def s1_clustered(geom: GridGeometry, n: int, seed: int, n_cells: int = 12000) -> np.ndarray:
+    """S1: ``n_cells`` distinct xy cells, heavy-tailed weights ``k^-0.8``; ~8 % of points fall outside in z."""
+    rng = np.random.default_rng(seed)
+    nx, ny = int(geom.grid_size[0]), int(geom.grid_size[1])
+    n_cells = min(n_cells, nx * ny)
+    cells = rng.choice(nx * ny, size=n_cells, replace=False)
+    w = np.arange(1, n_cells + 1, dtype=np.float64) ** -0.8
+    w /= w.sum()
+    pick = cells[rng.choice(n_cells, size=n, p=w)]
+    cx = (pick // ny).astype(np.float64)
+    cy = (pick % ny).astype(np.float64)
+    vs = geom.voxel_size.astype(np.float64)
+    off = geom.offset.astype(np.float64)
+    pts = np.empty((n, 4), dtype=np.float32)
+    pts[:, 0] = off[0] + (cx + rng.uniform(0.05, 0.95, n)) * vs[0]
+    pts[:, 1] = off[1] + (cy + rng.uniform(0.05, 0.95, n)) * vs[1]
+    zmin, zmax = float(geom.detection_range[2]), float(geom.detection_range[5])
+    pts[:, 2] = rng.uniform(zmin - 0.5, zmax + 0.5, n)
+    pts[:, 3] = rng.uniform(0.0, 1.0, n)
+    return pts
+
+
+def s2_ring(geom: GridGeometry, n: int, seed: int, beams: int = 64) -> np.ndarray:
+    """S2: spinning 64-beam LiDAR over flat ground, azimuth-major point order (exercises the max_voxels break)."""
+    rng = np.random.default_rng(seed)
+    steps = max(1, n // beams)
+    n_eff = steps * beams
+    elev = np.deg2rad(np.linspace(-24.8, 2.0, beams))
+    az = np.linspace(0.0, 2.0 * np.pi, steps, endpoint=False)
+    azg, elg = np.meshgrid(az, elev, indexing="ij")            # azimuth-major
+    azg, elg = azg.ravel(), elg.ravel()
+    sensor_h = 1.9
+    with np.errstate(divide="ignore", invalid="ignore"):
+        ground = np.where(elg < 0, sensor_h / np.maximum(np.sin(-elg), 1e-9), np.inf)
+    obstacle = 2.0 + rng.gamma(2.0, 15.0, n_eff)
+    rng_m = np.minimum(ground, obstacle)
+    rng_m *= 1.0 + 0.002 * rng.standard_normal(n_eff)
+    pts = np.empty((n_eff, 4), dtype=np.float32)
+    pts[:, 0] = rng_m * np.cos(elg) * np.cos(azg)
+    pts[:, 1] = rng_m * np.cos(elg) * np.sin(azg)
+    pts[:, 2] = sensor_h - 1.9 + rng_m * np.sin(elg)
+    pts[:, 3] = rng.uniform(0.0, 1.0, n_eff)
+    return pts
+
+
+def s3_uniform(geom: GridGeometry, n: int, seed: int) -> np.ndarray:
+    """S3: uniform over 1.1x the xy range (≈17 % outside); nearly every inside point opens a new cell."""
+    rng = np.random.default_rng(seed)
+    lo = geom.detection_range[:3].astype(np.float64)
+    hi = geom.detection_range[3:].astype(np.float64)
+    mid, half = (lo + hi) / 2, (hi - lo) / 2
+    pts = np.empty((n, 4), dtype=np.float32)
+    pts[:, 0] = rng.uniform(mid[0] - 1.1 * half[0], mid[0] + 1.1 * half[0], n)
+    pts[:, 1] = rng.uniform(mid[1] - 1.1 * half[1], mid[1] + 1.1 * half[1], n)
+    pts[:, 2] = rng.uniform(lo[2], hi[2], n)
+    pts[:, 3] = rng.uniform(0.0, 1.0, n)
+    return pts
+
+
+def edge_points(geom: GridGeometry) -> np.ndarray:
+    """S4 micro-cases: exact boundaries, signed zeros, non-finite and out-of-int32 values."""
+    lo = geom.detection_range[:3]
+    hi = geom.detection_range[3:]
+    f = np.float32
+    mid = ((lo + hi) / 2).astype(np.float32)
+    rows = [
+        [lo[0], lo[1], lo[2], 0.1],                                # lower corner: inside, cell (0,0,0)
+        [hi[0], hi[1], hi[2], 0.2],                                # upper corner: outside (exclusive)
+        [np.nextafter(hi[0], f(-np.inf)), np.nextafter(hi[1], f(-np.inf)), np.nextafter(hi[2], f(-np.inf)), 0.3],
+        [np.nextafter(lo[0], f(-np.inf)), mid[1], mid[2], 0.4],    # just below the lower bound
+        [f(-0.0), f(0.0), mid[2], 0.5],
+        [np.nan, mid[1], mid[2], 0.6],
+        [mid[0], np.inf, mid[2], 0.7],
+        [mid[0], mid[1], -np.inf, 0.8],
+        [3e9, mid[1], mid[2], 0.9],
+        [-3e9, mid[1], mid[2], 1.0],
+        [f(2.0 ** 32) * geom.voxel_size[0] + lo[0], mid[1], mid[2], 0.15],   # floor(...) = 2^32: not cell 0
+        [f(3.4e38), f(-3.4e38), mid[2], 0.25],
+        [mid[0], mid[1], mid[2], np.nan],                          # NaN intensity is payload, not geometry
+        [mid[0], mid[1], mid[2], 0.35],                            # same cell as the row above
+    ]
+    return np.asarray(rows, dtype=np.float32)
+
+
+def s4_edges(geom: GridGeometry, n: int, seed: int, n_cells: int = 12000) -> np.ndarray:
+    """S4: an S1 frame with the edge set spliced in at the front, the middle and the end."""
+    base = s1_clustered(geom, max(n, 8), seed, n_cells)
+    e = edge_points(geom)
+    h = base.shape[0] // 2
+    return np.ascontiguousarray(np.concatenate([e, base[:h], e[::-1], base[h:], e], axis=0))
+
+
+def make_frame(kind: str, geom: GridGeometry, n: int, seed: int, n_cells: int = 12000) -> np.ndarray:
+    kind = kind.upper()
+    if kind == "S1":
+        return s1_clustered(geom, n, seed, n_cells)
+    if kind == "S2":
+        return s2_ring(geom, n, seed)
+    if kind == "S3":
+        return s3_uniform(geom, n, seed)
+    if kind == "S4":
+        return s4_edges(geom, n, seed, n_cells)
+    raise ValueError(f"unknown synthetic frame kind {kind!r}")

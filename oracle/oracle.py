@@ -1,0 +1,192 @@
+"""ORACLE -- TEST INFRASTRUCTURE ONLY.  ctypes front of oracle/pillar_oracle.c plus numpy/torch mirrors.
+
+Only tests/, __graft_entry__.smoke() and bench.py's cpu_baseline / --impl reference legs may import this
+module, and only as the checker or the timed CPU baseline.  The product package
+(3d_object_detection_b200/) never imports it and fails loudly when its CUDA library is missing.
+
+Parity status: PINNED against outputs of the reference itself (tests/golden/, made by
+oracle/make_golden.py from /root/reference; checked by tests/test_oracle.py).
+"""
+from __future__ import annotations
+
+import ctypes as C
+from pathlib import Path
+
+import numpy as np
+
+from . import build as _build
+
+_LIB = None
+
+_f32p = np.ctypeslib.ndpointer(dtype=np.float32, flags="C_CONTIGUOUS")
+_i32p = np.ctypeslib.ndpointer(dtype=np.int32, flags="C_CONTIGUOUS")
+_i64p = np.ctypeslib.ndpointer(dtype=np.int64, flags="C_CONTIGUOUS")
+
+
+def lib():
+    global _LIB
+    if _LIB is None:
+        path = _build.LIB if _build.LIB.exists() else _build.build()
+        L = C.CDLL(str(path))
+        L.oracle_points_to_voxels.restype = C.c_int32
+        L.oracle_points_to_voxels.argtypes = [_f32p, C.c_int64, C.c_int32, _f32p, _i32p, _i32p, _i32p,
+                                              _f32p, _f32p, _i32p, C.c_int32, C.c_int32]
+        L.oracle_generate.restype = C.c_int32
+        L.oracle_generate.argtypes = [_f32p, C.c_int64, C.c_int32, _f32p, _i32p, _i32p,
+                                      _f32p, _f32p, _i32p, C.c_int32, C.c_int32]
+        L.oracle_decorate.restype = None
+        L.oracle_decorate.argtypes = [_f32p, _i32p, _i32p, C.c_int32, C.c_int64, C.c_int32, C.c_int32,
+                                      C.c_float, C.c_float, C.c_float, C.c_float, _f32p]
+        L.oracle_scatter.restype = None
+        L.oracle_scatter.argtypes = [_f32p, _i32p, C.c_int32, C.c_int64, C.c_int32, C.c_int32, C.c_int32,
+                                     C.c_int32, _f32p]
+        L.oracle_scatter_cmajor.restype = None
+        L.oracle_scatter_cmajor.argtypes = [_f32p, _i32p, C.c_int32, C.c_int64, C.c_int32, C.c_int32,
+                                            C.c_int32, _f32p]
+        L.oracle_frontend_batch.restype = C.c_int64
+        L.oracle_frontend_batch.argtypes = [_f32p, _i64p, C.c_int32, C.c_int32, _f32p, _f32p, _i32p,
+                                            C.c_int32, C.c_int32, C.c_float, C.c_float, C.c_float,
+                                            C.c_float, _f32p, C.c_int32, _f32p, _i32p, _i32p, _i32p,
+                                            _f32p, _f32p, C.c_int32]
+        _LIB = L
+    return _LIB
+
+
+def _geom_arrays(geom):
+    return (np.ascontiguousarray(geom.voxel_size, np.float32), np.ascontiguousarray(geom.offset, np.float32),
+            np.ascontiguousarray(geom.grid_size, np.int32))
+
+
+def generate(geom, points, max_voxels, max_points):
+    """VoxelGenerator.generate (framework/voxel_generator.py:28-40): returns (voxels, coors, num) sliced to V."""
+    points = np.ascontiguousarray(points, np.float32)
+    n, f = points.shape
+    vs, off, gs = _geom_arrays(geom)
+    voxels = np.empty((max_voxels, max_points, f), np.float32)
+    num = np.empty((max_voxels,), np.int32)
+    coors = np.empty((max_voxels, 3), np.int32)
+    v = lib().oracle_generate(points.reshape(-1) if n else np.zeros(1, np.float32), n, f,
+                              voxels.reshape(-1), num, coors.reshape(-1), vs, off, gs, max_voxels, max_points)
+    if v < 0:
+        raise MemoryError("oracle_generate: scratch grid allocation failed")
+    return voxels[:v], coors[:v], num[:v]
+
+
+def decorate_consts(voxel_size_cfg, offset):
+    """vx, vy, x_offset, y_offset exactly as PointNet.__init__ forms them (pointpillars8_shared.py:16-19):
+    vx, vy come from the *config list* (Python floats), the offsets from numpy fp32 (F13)."""
+    vx = voxel_size_cfg[0]
+    vy = voxel_size_cfg[1]
+    x_off = vx / 2 + offset[0]
+    y_off = vy / 2 + offset[1]
+    return float(np.float32(vx)), float(np.float32(vy)), float(np.float32(x_off)), float(np.float32(y_off))
+
+
+def decorate(voxels, num, coors, vx, vy, x_off, y_off):
+    """C oracle of pointpillars8_shared.py:32-54 -> (V,P,F+5) fp32."""
+    voxels = np.ascontiguousarray(voxels, np.float32)
+    num = np.ascontiguousarray(num, np.int32)
+    coors = np.ascontiguousarray(coors, np.int32)
+    v, p, f = voxels.shape
+    out = np.empty((v, p, f + 5), np.float32)
+    if v:
+        lib().oracle_decorate(voxels.reshape(-1), num, coors.reshape(-1), coors.shape[1], v, p, f,
+                              vx, vy, x_off, y_off, out.reshape(-1))
+    return out
+
+
+def decorate_numpy(voxels, num, coors, vx, vy, x_off, y_off):
+    """numpy fp32 mirror of the same op sequence as the torch code (sum over axis 1, divide, subtract,
+    multiply-then-add centre, concatenate, mask multiply) -- a second opinion on the C oracle."""
+    f32 = np.float32
+    voxels = np.asarray(voxels, f32)
+    mean = voxels[:, :, :3].sum(axis=1, keepdims=True, dtype=f32) / num.astype(f32).reshape(-1, 1, 1)
+    f_cluster = voxels[:, :, :3] - mean
+    f_center = np.zeros_like(voxels[:, :, :2])
+    f_center[:, :, 0] = voxels[:, :, 0] - (coors[:, 0].astype(f32)[:, None] * f32(vx) + f32(x_off))
+    f_center[:, :, 1] = voxels[:, :, 1] - (coors[:, 1].astype(f32)[:, None] * f32(vy) + f32(y_off))
+    feats = np.concatenate([voxels, f_cluster, f_center], axis=-1)
+    mask = (num.reshape(-1, 1) > np.arange(voxels.shape[1], dtype=np.int32).reshape(1, -1))
+    feats = feats * mask[..., None].astype(f32)
+    return feats
+
+
+def decorate_f64(voxels, num, coors, vx, vy, x_off, y_off):
+    """fp64 evaluation of the decoration: the yardstick both fp32 versions are held to."""
+    v64 = np.asarray(voxels, np.float64)
+    mean = v64[:, :, :3].sum(axis=1, keepdims=True) / num.astype(np.float64).reshape(-1, 1, 1)
+    fc = v64[:, :, :3] - mean
+    cx = coors[:, 0].astype(np.float64)[:, None] * float(np.float32(vx)) + float(np.float32(x_off))
+    cy = coors[:, 1].astype(np.float64)[:, None] * float(np.float32(vy)) + float(np.float32(y_off))
+    ce = np.stack([v64[:, :, 0] - cx, v64[:, :, 1] - cy], axis=-1)
+    feats = np.concatenate([v64, fc, ce], axis=-1)
+    mask = (num.reshape(-1, 1) > np.arange(v64.shape[1]).reshape(1, -1))
+    return feats * mask[..., None]
+
+
+def decorate_tolerance(voxels):
+    """Per-pillar absolute tolerance of the decoration parity check: 1e-6 relative to the
+    operand magnitude, i.e. 1e-6 * max(1, max |xyz| in the pillar), shape (V,1,1)."""
+    mag = np.abs(np.asarray(voxels)[:, :, :3]).reshape(len(voxels), -1)
+    mag = mag.max(axis=1) if mag.shape[1] else np.zeros(len(voxels))
+    return (1e-6 * np.maximum(1.0, mag)).reshape(-1, 1, 1)
+
+
+def scatter(feats, coors, nx, ny, batch=1):
+    """PointPillarsScatter.forward (pointpillars8_shared.py:76-111), row-major (V,C) features -> (B,C,nx,ny)."""
+    feats = np.ascontiguousarray(feats, np.float32)
+    coors = np.ascontiguousarray(coors, np.int32)
+    v, c = feats.shape
+    canvas = np.empty((batch, c, nx, ny), np.float32)
+    lib().oracle_scatter(feats.reshape(-1) if v else np.zeros(1, np.float32),
+                         coors.reshape(-1) if v else np.zeros(4, np.int32),
+                         coors.shape[1] if v else 3, v, c, nx, ny, batch, canvas.reshape(-1))
+    return canvas
+
+
+def scatter_cmajor(feats_cv, coors, nx, ny):
+    """Scatter.run (pointpillars8_export.py:44-51), channel-major (C,V) features -> (1,C,nx,ny)."""
+    feats_cv = np.ascontiguousarray(feats_cv, np.float32)
+    coors = np.ascontiguousarray(coors, np.int32)
+    c, v = feats_cv.shape
+    canvas = np.empty((1, c, nx, ny), np.float32)
+    lib().oracle_scatter_cmajor(feats_cv.reshape(-1) if v else np.zeros(1, np.float32),
+                                coors.reshape(-1) if v else np.zeros(4, np.int32),
+                                coors.shape[1] if v else 3, v, c, nx, ny, canvas.reshape(-1))
+    return canvas
+
+
+def scatter_backward(grad_canvas, coors, batch=1):
+    """Gradient of the scatter w.r.t. voxel_features (autograd of index_put): a gather."""
+    g = np.asarray(grad_canvas, np.float32)
+    b, c, nx, ny = g.shape
+    coors = np.asarray(coors)
+    bi = coors[:, 3] if coors.shape[1] >= 4 else np.zeros(len(coors), np.int64)
+    return np.ascontiguousarray(g[bi, :, coors[:, 0], coors[:, 1]])
+
+
+class FrontendBatch:
+    """Reusable buffers + call of oracle_frontend_batch (bench.py CPU baseline body)."""
+
+    def __init__(self, geom, max_voxels, max_points, n_feat, n_frames, n_ch=64):
+        self.geom, self.mv, self.mp, self.f, self.b, self.c = geom, max_voxels, max_points, n_feat, n_frames, n_ch
+        nx, ny = int(geom.grid_size[0]), int(geom.grid_size[1])
+        self.voxels = np.empty((n_frames, max_voxels, max_points, n_feat), np.float32)
+        self.num = np.empty((n_frames, max_voxels), np.int32)
+        self.coors = np.empty((n_frames, max_voxels, 3), np.int32)
+        self.voxel_num = np.zeros((n_frames,), np.int32)
+        self.features = np.empty((n_frames, max_voxels, max_points, n_feat + 5), np.float32)
+        self.canvas = np.empty((n_frames, n_ch, nx, ny), np.float32)
+
+    def run(self, points_cat, frame_offsets, consts, pillar_feats, n_threads):
+        vs, off, gs = _geom_arrays(self.geom)
+        vx, vy, xo, yo = consts
+        tot = lib().oracle_frontend_batch(
+            np.ascontiguousarray(points_cat, np.float32).reshape(-1),
+            np.ascontiguousarray(frame_offsets, np.int64), self.b, self.f, vs, off, gs, self.mv, self.mp,
+            vx, vy, xo, yo, np.ascontiguousarray(pillar_feats, np.float32).reshape(-1), self.c,
+            self.voxels.reshape(-1), self.num.reshape(-1), self.coors.reshape(-1), self.voxel_num,
+            self.features.reshape(-1), self.canvas.reshape(-1), int(n_threads))
+        if tot < 0:
+            raise MemoryError("oracle_frontend_batch: allocation failed")
+        return int(tot)

@@ -1,0 +1,55 @@
+"""Shared helpers for the test-suite: golden fixtures, hashing, synthetic frames."""
+import hashlib
+import importlib
+import json
+from pathlib import Path
+
+import numpy as np
+
+GOLD = Path(__file__).resolve().parent / "golden"
+cfgmod = importlib.import_module("3d_object_detection_b200.config")
+synth = importlib.import_module("3d_object_detection_b200.synth")
+
+GRID_KEYS = sorted(cfgmod.GRIDS)
+SMALL_NAMES = ["s1", "s1_overflow", "s3_overflow", "s2_ring", "s4_edges", "dense_cap", "n0", "n5"]
+
+
+def sha(a):
+    a = np.ascontiguousarray(a)
+    return hashlib.sha256(a.view(np.uint8).reshape(-1).tobytes() if a.size else b"").hexdigest()
+
+
+def load_small(gkey, name):
+    z = np.load(GOLD / f"small_{gkey}_{name}.npz")
+    return {k: z[k] for k in z.files}
+
+
+def small_config(gkey, g):
+    cfg = cfgmod.builtin_config(gkey)
+    cfg["max_voxels"] = int(g["max_voxels"])
+    cfg["max_num_points"] = int(g["max_points"])
+    return cfg
+
+
+def full_hashes():
+    return json.loads((GOLD / "full_hashes.json").read_text())
+
+
+def full_frame(gkey, kind):
+    """Regenerate the seeded full-size frame a full_hashes.json entry was made from."""
+    h = full_hashes()[f"{gkey}/{kind}"]
+    cfg = cfgmod.builtin_config(gkey)
+    geom = cfgmod.derive_grid(cfg)
+    pts = synth.make_frame(kind, geom, cfg["frame_points"], h["seed"], synth.S1_CELLS[gkey])
+    return cfg, geom, pts, h
+
+
+def assert_vox_equal(got, want, what=""):
+    gv, gc, gn = got
+    wv, wc, wn = want
+    assert gn.shape == wn.shape, f"{what}: voxel count {gn.shape} != {wn.shape}"
+    assert np.array_equal(gn, wn), f"{what}: num_points_per_voxel differs"
+    assert np.array_equal(gc, wc), f"{what}: coors differ"
+    # bit-exact incl. NaN payloads: compare raw words
+    assert np.array_equal(np.ascontiguousarray(gv).view(np.uint32), np.ascontiguousarray(wv).view(np.uint32)), \
+        f"{what}: voxels differ"
