@@ -9,4 +9,22 @@ The directory name is not a Python identifier; import it as ``pillarfront`` (rep
 """
 from .config import GRIDS, CONFIG_GRID, GridGeometry, builtin_config, derive_grid, load_config  # noqa: F401
 
-__all__ = ["GRIDS", "CONFIG_GRID", "GridGeometry", "builtin_config", "derive_grid", "load_config"]
+_LAZY = {
+    "VoxelGenerator": "voxel_generator", "VoxelGenerator_trt": "voxel_generator",
+    "decorate": "pillar_ops", "decorate_constants": "pillar_ops", "PointNet": "pillar_ops",
+    "PointPillarsScatter": "pillar_ops", "Scatter": "pillar_ops", "Scatter_cuda": "pillar_ops",
+    "PillarFrontEnd": "frontend", "shard_frames": "sharding", "PillarFrontError": "_lib",
+}
+
+__all__ = ["GRIDS", "CONFIG_GRID", "GridGeometry", "builtin_config", "derive_grid", "load_config", *_LAZY]
+
+
+def __getattr__(name):
+    # torch-dependent modules load on first use so config/synth helpers stay importable anywhere
+    if name in _LAZY:
+        import importlib
+        mod = importlib.import_module(f"{__name__}.{_LAZY[name]}")
+        val = getattr(mod, name)
+        globals()[name] = val
+        return val
+    raise AttributeError(f"module {__name__!r} has no attribute {name!r}")

@@ -1,0 +1,117 @@
+"""ctypes binding of libpillarfront.so (C ABI: include/pillarfront.h).
+
+There is no fallback: if the CUDA library is missing or a call fails, this raises.
+"""
+from __future__ import annotations
+
+import ctypes as C
+from pathlib import Path
+
+LIB_PATH = Path(__file__).resolve().parent / "lib" / "libpillarfront.so"
+
+EXPORTS = ["pf_version", "pf_last_error_string", "pf_create", "pf_destroy", "pf_workspace_bytes",
+           "pf_voxelize", "pf_voxelize_decorate", "pf_decorate", "pf_scatter", "pf_scatter_from_map",
+           "pf_scatter_backward"]
+
+
+class GridDesc(C.Structure):
+    """pf_grid_desc"""
+    _fields_ = [("offset", C.c_float * 3), ("voxel_size", C.c_float * 3), ("grid", C.c_int32 * 3),
+                ("max_voxels", C.c_int32), ("max_points", C.c_int32), ("num_features", C.c_int32)]
+
+
+class PillarFrontError(RuntimeError):
+    pass
+
+
+_lib = None
+_p = C.c_void_p
+
+
+def load():
+    """Load the shared library once; raise loudly if it has not been built."""
+    global _lib
+    if _lib is not None:
+        return _lib
+    if not LIB_PATH.exists():
+        raise PillarFrontError(
+            f"{LIB_PATH} is missing: build it with __graft_entry__.build() "
+            "(python -c 'import __graft_entry__ as g; g.build()'). There is no CPU fallback.")
+    L = C.CDLL(str(LIB_PATH))
+    L.pf_version.restype = C.c_int
+    L.pf_version.argtypes = []
+    L.pf_last_error_string.restype = C.c_char_p
+    L.pf_last_error_string.argtypes = []
+    L.pf_create.restype = C.c_int
+    L.pf_create.argtypes = [C.POINTER(GridDesc), C.c_int, C.c_int, C.c_int, C.POINTER(_p)]
+    L.pf_destroy.restype = C.c_int
+    L.pf_destroy.argtypes = [_p]
+    L.pf_workspace_bytes.restype = C.c_size_t
+    L.pf_workspace_bytes.argtypes = [_p]
+    L.pf_voxelize.restype = C.c_int
+    L.pf_voxelize.argtypes = [_p, _p, _p, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, _p, _p, _p, _p, _p]
+    L.pf_voxelize_decorate.restype = C.c_int
+    L.pf_voxelize_decorate.argtypes = [_p, _p, _p, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int,
+                                       C.c_float, C.c_float, C.c_float, C.c_float, C.c_int,
+                                       _p, _p, _p, _p, _p, _p]
+    L.pf_decorate.restype = C.c_int
+    L.pf_decorate.argtypes = [_p, _p, _p, C.c_int, C.c_int64, C.c_int, C.c_int,
+                              C.c_float, C.c_float, C.c_float, C.c_float, _p, _p]
+    L.pf_scatter.restype = C.c_int
+    L.pf_scatter.argtypes = [_p, _p, C.c_int64, C.c_int64, _p, C.c_int, C.c_int64, C.c_int, C.c_int, _p, _p]
+    L.pf_scatter_from_map.restype = C.c_int
+    L.pf_scatter_from_map.argtypes = [_p, _p, C.c_int64, C.c_int64, C.c_int, C.c_int, C.c_int, _p, _p]
+    L.pf_scatter_backward.restype = C.c_int
+    L.pf_scatter_backward.argtypes = [_p, _p, C.c_int, C.c_int64, C.c_int, C.c_int, C.c_int, C.c_int, _p,
+                                      C.c_int64, C.c_int64, _p]
+    _lib = L
+    return L
+
+
+def check(rc: int, what: str = "") -> None:
+    if rc != 0:
+        msg = load().pf_last_error_string().decode("utf-8", "replace")
+        raise PillarFrontError(f"{what or 'libpillarfront'} failed (status {rc}): {msg}")
+
+
+def make_desc(geom, max_voxels: int, max_points: int, num_features: int) -> GridDesc:
+    d = GridDesc()
+    for k in range(3):
+        d.offset[k] = float(geom.offset[k])
+        d.voxel_size[k] = float(geom.voxel_size[k])
+        d.grid[k] = int(geom.grid_size[k])
+    d.max_voxels, d.max_points, d.num_features = int(max_voxels), int(max_points), int(num_features)
+    return d
+
+
+class Handle:
+    """Owns one pf_handle (workspace bound to one device; use one per stream)."""
+
+    def __init__(self, geom, max_voxels, max_points, num_features, max_frames, max_points_per_frame, device):
+        self.lib = load()
+        self.desc = make_desc(geom, max_voxels, max_points, num_features)
+        self.max_frames = int(max_frames)
+        self.max_points_per_frame = int(max_points_per_frame)
+        self.device = int(device)
+        self._h = _p()
+        check(self.lib.pf_create(C.byref(self.desc), self.max_frames, self.max_points_per_frame,
+                                 self.device, C.byref(self._h)), "pf_create")
+
+    @property
+    def ptr(self):
+        return self._h
+
+    @property
+    def workspace_bytes(self) -> int:
+        return int(self.lib.pf_workspace_bytes(self._h))
+
+    def close(self):
+        if self._h:
+            self.lib.pf_destroy(self._h)
+            self._h = _p()
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass

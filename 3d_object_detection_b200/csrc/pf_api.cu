@@ -1,0 +1,256 @@
+// C-ABI layer of libpillarfront.so: handle life-cycle, argument validation, error reporting.
+// Declarations and the reference functions each entry point replaces: include/pillarfront.h.
+#include <cstdarg>
+#include <cstdio>
+#include <new>
+#include <string>
+
+#include "pf_internal.cuh"
+
+struct pf_handle {
+    pf::Params p;
+    pf::Work w;
+    pf_grid_desc desc;
+    int device;
+    int max_frames;
+    int max_points_per_frame;
+    size_t bytes;
+    void *slab;   // one allocation, carved into the Work arrays
+};
+
+namespace {
+
+thread_local std::string g_err = "";
+
+int fail(int code, const char *fmt, ...) __attribute__((format(printf, 2, 3)));
+int fail(int code, const char *fmt, ...)
+{
+    char buf[512];
+    va_list ap;
+    va_start(ap, fmt);
+    vsnprintf(buf, sizeof buf, fmt, ap);
+    va_end(ap);
+    g_err = buf;
+    return code;
+}
+
+int cuda_fail(cudaError_t e, const char *what)
+{
+    g_err = std::string(what) + ": " + cudaGetErrorName(e) + " (" + cudaGetErrorString(e) + ")";
+    return (int)e;
+}
+
+inline size_t align_up(size_t x, size_t a) { return (x + a - 1) / a * a; }
+
+bool aligned16(const void *p) { return (reinterpret_cast<uintptr_t>(p) & 15) == 0; }
+
+struct DeviceGuard {
+    int prev = -1;
+    bool switched = false;
+    explicit DeviceGuard(int dev)
+    {
+        if (cudaGetDevice(&prev) == cudaSuccess && prev != dev) switched = (cudaSetDevice(dev) == cudaSuccess);
+    }
+    ~DeviceGuard()
+    {
+        if (switched) cudaSetDevice(prev);
+    }
+};
+
+}  // namespace
+
+extern "C" {
+
+int pf_version(void) { return PF_VERSION; }
+
+const char *pf_last_error_string(void) { return g_err.c_str(); }
+
+int pf_create(const pf_grid_desc *d, int max_frames, int max_points_per_frame, int device, pf_handle **out)
+{
+    if (!d || !out) return fail(PF_ERR_INVALID_ARGUMENT, "pf_create: null argument");
+    *out = nullptr;
+    if (max_frames < 1 || max_frames > 65535) return fail(PF_ERR_INVALID_ARGUMENT, "pf_create: max_frames %d out of [1, 65535]", max_frames);
+    if (max_points_per_frame < 1) return fail(PF_ERR_INVALID_ARGUMENT, "pf_create: max_points_per_frame must be >= 1");
+    for (int k = 0; k < 3; ++k) {
+        if (!(d->voxel_size[k] > 0.f)) return fail(PF_ERR_INVALID_ARGUMENT, "pf_create: voxel_size[%d] must be > 0", k);
+        if (d->grid[k] < 1 || d->grid[k] >= (1 << 24)) return fail(PF_ERR_INVALID_ARGUMENT, "pf_create: grid[%d]=%d out of [1, 2^24)", k, d->grid[k]);
+    }
+    const long long cells = (long long)d->grid[0] * d->grid[1] * d->grid[2];
+    if (cells >= (1ll << 31)) return fail(PF_ERR_UNSUPPORTED, "pf_create: %lld cells do not fit int32", cells);
+    if (d->max_voxels < 1 || d->max_voxels >= (1 << 23)) return fail(PF_ERR_INVALID_ARGUMENT, "pf_create: max_voxels %d out of [1, 2^23)", d->max_voxels);
+    if (d->max_points < 1) return fail(PF_ERR_INVALID_ARGUMENT, "pf_create: max_points must be >= 1");
+    if (d->max_points > pf::kCountCap) return fail(PF_ERR_UNSUPPORTED, "pf_create: max_points %d > %d", d->max_points, pf::kCountCap);
+    if (d->num_features < 3 || d->num_features > 16) return fail(PF_ERR_UNSUPPORTED, "pf_create: num_features %d outside 3..16", d->num_features);
+
+    if (device < 0) {
+        cudaError_t e = cudaGetDevice(&device);
+        if (e != cudaSuccess) return cuda_fail(e, "pf_create: cudaGetDevice");
+    }
+    DeviceGuard guard(device);
+
+    pf_handle *h = new (std::nothrow) pf_handle();
+    if (!h) return fail(PF_ERR_OUT_OF_MEMORY, "pf_create: host allocation failed");
+    h->desc = *d;
+    h->device = device;
+    h->max_frames = max_frames;
+    h->max_points_per_frame = max_points_per_frame;
+    pf::Params &p = h->p;
+    for (int k = 0; k < 3; ++k) p.off[k] = d->offset[k], p.vs[k] = d->voxel_size[k];
+    p.nx = d->grid[0], p.ny = d->grid[1], p.nz = d->grid[2];
+    p.cells = (int)cells;
+    p.plane = d->grid[0] * d->grid[1];
+    p.max_voxels = d->max_voxels;
+    p.P = d->max_points;
+    p.F = d->num_features;
+    p.npts_cap = (int)align_up((size_t)max_points_per_frame, pf::kTile);
+    p.tiles_cap = p.npts_cap / pf::kTile;
+    p.vcols = (int)align_up((size_t)d->max_voxels, 16);
+    if ((size_t)p.vcols > 200 * 1024) { delete h; return fail(PF_ERR_UNSUPPORTED, "pf_create: max_voxels %d too large for the tile table", d->max_voxels); }
+
+    const size_t B = (size_t)max_frames;
+    size_t off = 0;
+    auto carve = [&](size_t bytes) { size_t o = off; off = align_up(off + bytes, 256); return o; };
+    const size_t o_grid = carve(B * p.cells * 4), o_cell = carve(B * p.npts_cap * 4), o_vr = carve(B * p.npts_cap * 4);
+    const size_t o_tc = carve(B * p.tiles_cap * 4), o_cnt = carve(B * p.tiles_cap * (size_t)p.vcols);
+    const size_t o_slot = carve(B * p.max_voxels * (size_t)p.P * 4), o_vcell = carve(B * p.max_voxels * 4);
+    const size_t o_vcount = carve(B * p.max_voxels * 4), o_istar = carve(B * 4), o_vnum = carve(B * 4);
+    const size_t o_map = carve(B * p.plane * 4);
+    h->bytes = off;
+    cudaError_t e = cudaMalloc(&h->slab, h->bytes);
+    if (e != cudaSuccess) { delete h; cudaGetLastError(); return fail(PF_ERR_OUT_OF_MEMORY, "pf_create: cudaMalloc of %zu bytes failed", off); }
+    char *base = static_cast<char *>(h->slab);
+    pf::Work &w = h->w;
+    w.grid = reinterpret_cast<int32_t *>(base + o_grid);
+    w.cellid = reinterpret_cast<int32_t *>(base + o_cell);
+    w.vr = reinterpret_cast<int32_t *>(base + o_vr);
+    w.tilecnt = reinterpret_cast<int32_t *>(base + o_tc);
+    w.cnt = reinterpret_cast<uint8_t *>(base + o_cnt);
+    w.slotidx = reinterpret_cast<int32_t *>(base + o_slot);
+    w.vcell = reinterpret_cast<int32_t *>(base + o_vcell);
+    w.vcount = reinterpret_cast<int32_t *>(base + o_vcount);
+    w.istar = reinterpret_cast<int32_t *>(base + o_istar);
+    w.vnum = reinterpret_cast<int32_t *>(base + o_vnum);
+    w.map = reinterpret_cast<int32_t *>(base + o_map);
+    // one-time initialisation: the kernels put the grid / map back themselves after every call
+    e = cudaMemsetAsync(h->slab, 0, h->bytes, 0);
+    if (e == cudaSuccess) e = pf::launch_fill_i32(w.grid, pf::kEmpty, B * p.cells, 0);
+    if (e == cudaSuccess) e = pf::launch_fill_i32(w.map, -1, B * p.plane, 0);
+    if (e == cudaSuccess) e = cudaStreamSynchronize(0);
+    if (e != cudaSuccess) { cudaFree(h->slab); delete h; return cuda_fail(e, "pf_create: workspace initialisation"); }
+    *out = h;
+    return PF_OK;
+}
+
+int pf_destroy(pf_handle *h)
+{
+    if (!h) return PF_OK;
+    DeviceGuard guard(h->device);
+    cudaError_t e = cudaFree(h->slab);
+    delete h;
+    return e == cudaSuccess ? PF_OK : cuda_fail(e, "pf_destroy: cudaFree");
+}
+
+size_t pf_workspace_bytes(const pf_handle *h) { return h ? h->bytes : 0; }
+
+static int voxelize_common(pf_handle *h, const pf::VoxelizeArgs &a, void *stream, const char *who)
+{
+    if (!h) return fail(PF_ERR_INVALID_ARGUMENT, "%s: null handle", who);
+    if (a.n_frames < 0) return fail(PF_ERR_INVALID_ARGUMENT, "%s: n_frames < 0", who);
+    if (a.n_frames == 0) return PF_OK;
+    if (a.n_frames > h->max_frames) return fail(PF_ERR_CAPACITY, "%s: n_frames %d > handle capacity %d", who, a.n_frames, h->max_frames);
+    if (a.max_frame_points < 0 || a.max_frame_points > h->max_points_per_frame)
+        return fail(PF_ERR_CAPACITY, "%s: max_frame_points %d outside [0, %d]", who, a.max_frame_points, h->max_points_per_frame);
+    if (!a.frame_offsets || (!a.points && a.max_frame_points > 0)) return fail(PF_ERR_INVALID_ARGUMENT, "%s: null points/frame_offsets", who);
+    if (a.point_stride < h->p.F) return fail(PF_ERR_INVALID_ARGUMENT, "%s: point_stride %d < num_features %d", who, a.point_stride, h->p.F);
+    if (a.coors_stride != 3 && a.coors_stride != 4) return fail(PF_ERR_INVALID_ARGUMENT, "%s: coors_stride must be 3 or 4", who);
+    if (!a.voxel_num) return fail(PF_ERR_INVALID_ARGUMENT, "%s: voxel_num must not be null", who);
+    if (a.voxels && !aligned16(a.voxels)) return fail(PF_ERR_INVALID_ARGUMENT, "%s: voxels must be 16-byte aligned", who);
+    if (a.features && !aligned16(a.features)) return fail(PF_ERR_INVALID_ARGUMENT, "%s: features must be 16-byte aligned", who);
+    if (a.keep_cell_map && h->p.nz != 1) return fail(PF_ERR_UNSUPPORTED, "%s: keep_cell_map needs nz == 1", who);
+    DeviceGuard guard(h->device);
+    cudaError_t e = pf::launch_voxelize(h->p, h->w, a, static_cast<cudaStream_t>(stream));
+    return e == cudaSuccess ? PF_OK : cuda_fail(e, who);
+}
+
+int pf_voxelize(pf_handle *h, const float *points, const int32_t *frame_offsets, int n_frames, int max_frame_points,
+                int point_stride, int compact, int coors_stride, float *voxels, int32_t *coors, int32_t *num_points,
+                int32_t *voxel_num, void *stream)
+{
+    pf::VoxelizeArgs a{};
+    a.points = points, a.frame_offsets = frame_offsets, a.n_frames = n_frames, a.max_frame_points = max_frame_points;
+    a.point_stride = point_stride, a.compact = compact, a.coors_stride = coors_stride;
+    a.voxels = voxels, a.coors = coors, a.num_points = num_points, a.voxel_num = voxel_num;
+    return voxelize_common(h, a, stream, "pf_voxelize");
+}
+
+int pf_voxelize_decorate(pf_handle *h, const float *points, const int32_t *frame_offsets, int n_frames,
+                         int max_frame_points, int point_stride, int compact, int coors_stride, float vx, float vy,
+                         float x_off, float y_off, int keep_cell_map, float *voxels, int32_t *coors,
+                         int32_t *num_points, int32_t *voxel_num, float *features, void *stream)
+{
+    pf::VoxelizeArgs a{};
+    a.points = points, a.frame_offsets = frame_offsets, a.n_frames = n_frames, a.max_frame_points = max_frame_points;
+    a.point_stride = point_stride, a.compact = compact, a.coors_stride = coors_stride;
+    a.vx = vx, a.vy = vy, a.x_off = x_off, a.y_off = y_off, a.keep_cell_map = keep_cell_map;
+    a.voxels = voxels, a.coors = coors, a.num_points = num_points, a.voxel_num = voxel_num, a.features = features;
+    return voxelize_common(h, a, stream, "pf_voxelize_decorate");
+}
+
+int pf_decorate(const float *voxels, const int32_t *num_points, const int32_t *coors, int coors_stride,
+                int64_t n_voxels, int max_points, int num_features, float vx, float vy, float x_off, float y_off,
+                float *features, void *stream)
+{
+    if (n_voxels < 0) return fail(PF_ERR_INVALID_ARGUMENT, "pf_decorate: n_voxels < 0");
+    if (n_voxels == 0) return PF_OK;
+    if (!voxels || !num_points || !coors || !features) return fail(PF_ERR_INVALID_ARGUMENT, "pf_decorate: null argument");
+    if (coors_stride < 2) return fail(PF_ERR_INVALID_ARGUMENT, "pf_decorate: coors_stride must be >= 2");
+    if (max_points < 1 || max_points > 4096) return fail(PF_ERR_UNSUPPORTED, "pf_decorate: max_points %d outside 1..4096", max_points);
+    if (num_features < 3 || num_features > 16) return fail(PF_ERR_UNSUPPORTED, "pf_decorate: num_features %d outside 3..16", num_features);
+    if (!aligned16(features)) return fail(PF_ERR_INVALID_ARGUMENT, "pf_decorate: features must be 16-byte aligned");
+    cudaError_t e = pf::launch_decorate(voxels, num_points, coors, coors_stride, n_voxels, max_points, num_features, vx, vy,
+                                        x_off, y_off, features, static_cast<cudaStream_t>(stream));
+    return e == cudaSuccess ? PF_OK : cuda_fail(e, "pf_decorate");
+}
+
+int pf_scatter(pf_handle *h, const float *feats, int64_t feat_stride_v, int64_t feat_stride_c, const int32_t *coors,
+               int coors_stride, int64_t n_voxels, int batch, int n_ch, float *canvas, void *stream)
+{
+    if (!h || !canvas) return fail(PF_ERR_INVALID_ARGUMENT, "pf_scatter: null handle/canvas");
+    if (n_voxels < 0 || n_voxels >= (1ll << 31)) return fail(PF_ERR_INVALID_ARGUMENT, "pf_scatter: n_voxels out of range");
+    if (n_voxels > 0 && (!feats || !coors)) return fail(PF_ERR_INVALID_ARGUMENT, "pf_scatter: null feats/coors");
+    if (coors_stride < 2) return fail(PF_ERR_INVALID_ARGUMENT, "pf_scatter: coors_stride must be >= 2");
+    if (batch < 1 || batch > h->max_frames) return fail(PF_ERR_CAPACITY, "pf_scatter: batch %d outside [1, %d]", batch, h->max_frames);
+    if (n_ch < 1) return fail(PF_ERR_INVALID_ARGUMENT, "pf_scatter: n_ch < 1");
+    DeviceGuard guard(h->device);
+    cudaError_t e = pf::launch_scatter(h->p, h->w, feats, feat_stride_v, feat_stride_c, coors, coors_stride, n_voxels,
+                                       batch, n_ch, canvas, static_cast<cudaStream_t>(stream));
+    return e == cudaSuccess ? PF_OK : cuda_fail(e, "pf_scatter");
+}
+
+int pf_scatter_from_map(pf_handle *h, const float *feats, int64_t feat_stride_v, int64_t feat_stride_c, int n_frames,
+                        int compact, int n_ch, float *canvas, void *stream)
+{
+    if (!h || !canvas || !feats) return fail(PF_ERR_INVALID_ARGUMENT, "pf_scatter_from_map: null argument");
+    if (h->p.nz != 1) return fail(PF_ERR_UNSUPPORTED, "pf_scatter_from_map: needs nz == 1");
+    if (n_frames < 1 || n_frames > h->max_frames) return fail(PF_ERR_CAPACITY, "pf_scatter_from_map: n_frames %d outside [1, %d]", n_frames, h->max_frames);
+    if (n_ch < 1) return fail(PF_ERR_INVALID_ARGUMENT, "pf_scatter_from_map: n_ch < 1");
+    DeviceGuard guard(h->device);
+    cudaError_t e = pf::launch_scatter_from_map(h->p, h->w, feats, feat_stride_v, feat_stride_c, n_frames, compact, n_ch,
+                                                canvas, static_cast<cudaStream_t>(stream));
+    return e == cudaSuccess ? PF_OK : cuda_fail(e, "pf_scatter_from_map");
+}
+
+int pf_scatter_backward(const float *grad_canvas, const int32_t *coors, int coors_stride, int64_t n_voxels, int batch,
+                        int n_ch, int nx, int ny, float *grad_feats, int64_t feat_stride_v, int64_t feat_stride_c,
+                        void *stream)
+{
+    if (n_voxels < 0) return fail(PF_ERR_INVALID_ARGUMENT, "pf_scatter_backward: n_voxels < 0");
+    if (n_voxels == 0) return PF_OK;
+    if (!grad_canvas || !coors || !grad_feats) return fail(PF_ERR_INVALID_ARGUMENT, "pf_scatter_backward: null argument");
+    if (coors_stride < 2 || batch < 1 || n_ch < 1 || nx < 1 || ny < 1) return fail(PF_ERR_INVALID_ARGUMENT, "pf_scatter_backward: bad sizes");
+    cudaError_t e = pf::launch_scatter_backward(grad_canvas, coors, coors_stride, n_voxels, batch, n_ch, nx, ny, grad_feats,
+                                                feat_stride_v, feat_stride_c, static_cast<cudaStream_t>(stream));
+    return e == cudaSuccess ? PF_OK : cuda_fail(e, "pf_scatter_backward");
+}
+
+}  // extern "C"

@@ -1,0 +1,112 @@
+// Internal declarations shared by the kernels and the C-ABI layer of libpillarfront.so (sm_100a only).
+#pragma once
+
+#include <cuda_runtime.h>
+#include <stdint.h>
+
+#include "pillarfront.h"
+
+namespace pf {
+
+constexpr int kEmpty = 0x7fffffff;   // grid cell never touched this frame
+constexpr int kTileWarps = 8;        // warps per tile CTA in k_tile_rank
+constexpr int kTileSteps = 8;        // 32-point steps each warp owns, in point order
+constexpr int kTile = kTileWarps * kTileSteps * 32;   // 2048 points per tile
+constexpr int kCountCap = 255;       // saturation of the per-(tile,voxel) byte counters (>= max_points)
+
+// Geometry and capacities, passed by value to every kernel.
+struct Params {
+    float off[3];
+    float vs[3];
+    int nx, ny, nz;
+    int cells;        // nx*ny*nz
+    int plane;        // nx*ny
+    int max_voxels;
+    int P;            // max points per voxel
+    int F;            // floats per point
+    int npts_cap;     // per-frame stride of the per-point scratch arrays (multiple of kTile)
+    int tiles_cap;    // npts_cap / kTile
+    int vcols;        // row stride of the count matrix (max_voxels rounded up to 16)
+};
+
+// Device scratch owned by a handle.  Nothing here is API-visible; none of it counts as algorithmic bytes.
+struct Work {
+    int32_t *grid;      // [B][cells]   kEmpty | first point index (>=0) | ~voxel_id (<0)
+    int32_t *cellid;    // [B][npts_cap] linear cell per point, -1 outside
+    int32_t *vr;        // [B][npts_cap] (voxel_id << 8 | in-tile rank), -1 if dropped
+    int32_t *tilecnt;   // [B][tiles_cap] creators per tile
+    uint8_t *cnt;       // [B][tiles_cap][vcols] points per (tile, voxel), then its exclusive column scan
+    int32_t *slotidx;   // [B][max_voxels][P] point index held by each voxel slot
+    int32_t *vcell;     // [B][max_voxels] linear cell of each voxel
+    int32_t *vcount;    // [B][max_voxels] min(points in voxel, P)
+    int32_t *istar;     // [B] cut-off index i*: first point index the sequential loop never reaches
+    int32_t *vnum;      // [B] voxels per frame
+    int32_t *map;       // [B][plane] cell -> feature row for the stand-alone scatter, -1 = none
+};
+
+struct VoxelizeArgs {
+    const float *points;
+    const int32_t *frame_offsets;
+    int n_frames;
+    int max_frame_points;
+    int point_stride;
+    int compact;
+    int coors_stride;
+    float vx, vy, x_off, y_off;
+    int keep_cell_map;
+    float *voxels;
+    int32_t *coors;
+    int32_t *num_points;
+    int32_t *voxel_num;
+    float *features;
+};
+
+// launchers (pf_voxelize.cu / pf_scatter.cu); all asynchronous on `stream`, return the launch error.
+cudaError_t launch_fill_i32(int32_t *dst, int32_t value, size_t n, cudaStream_t stream);
+cudaError_t launch_voxelize(const Params &p, const Work &w, const VoxelizeArgs &a, cudaStream_t stream);
+cudaError_t launch_decorate(const float *voxels, const int32_t *num, const int32_t *coors, int coors_stride,
+                            int64_t n_voxels, int P, int F, float vx, float vy, float x_off, float y_off,
+                            float *features, cudaStream_t stream);
+cudaError_t launch_scatter(const Params &p, const Work &w, const float *feats, int64_t sv, int64_t sc,
+                           const int32_t *coors, int coors_stride, int64_t n_voxels, int batch, int n_ch,
+                           float *canvas, cudaStream_t stream);
+cudaError_t launch_scatter_from_map(const Params &p, const Work &w, const float *feats, int64_t sv, int64_t sc,
+                                    int n_frames, int compact, int n_ch, float *canvas, cudaStream_t stream);
+cudaError_t launch_scatter_backward(const float *grad_canvas, const int32_t *coors, int coors_stride,
+                                    int64_t n_voxels, int batch, int n_ch, int nx, int ny, float *grad_feats,
+                                    int64_t sv, int64_t sc, cudaStream_t stream);
+
+// ---- small device helpers -------------------------------------------------------------------------------
+#ifdef __CUDACC__
+
+// Linear cell of a point, or -1 if outside.  Bit-exact restatement of framework/voxel_generator.py:90-91:
+// fp32 subtract, IEEE fp32 divide, floor, and a range test that NaN / +-Inf / out-of-int32 values fail
+// (SURVEY.md F4, F7).  The intrinsics pin round-to-nearest and forbid FMA contraction / fast division.
+__device__ __forceinline__ int cell_of_point(float x, float y, float z, const Params &p)
+{
+    const float qx = floorf(__fdiv_rn(__fsub_rn(x, p.off[0]), p.vs[0]));
+    const float qy = floorf(__fdiv_rn(__fsub_rn(y, p.off[1]), p.vs[1]));
+    const float qz = floorf(__fdiv_rn(__fsub_rn(z, p.off[2]), p.vs[2]));
+    const bool in = (qx >= 0.f) && (qx < (float)p.nx) && (qy >= 0.f) && (qy < (float)p.ny) && (qz >= 0.f) &&
+                    (qz < (float)p.nz);
+    if (!in) return -1;
+    return ((int)qx * p.ny + (int)qy) * p.nz + (int)qz;
+}
+
+__device__ __forceinline__ unsigned lanemask_lt()
+{
+    unsigned m;
+    asm("mov.u32 %0, %%lanemask_lt;" : "=r"(m));
+    return m;
+}
+
+// streaming (evict-first) 16-byte store: canvas lines are written once and never re-read by this library
+__device__ __forceinline__ void st_cs_f4(float *ptr, float a, float b, float c, float d)
+{
+    asm volatile("st.global.cs.v4.f32 [%0], {%1, %2, %3, %4};" ::"l"(ptr), "f"(a), "f"(b), "f"(c), "f"(d)
+                 : "memory");
+}
+
+#endif  // __CUDACC__
+
+}  // namespace pf

@@ -1,0 +1,140 @@
+"""Batched, device-resident front end: voxelise -> decorate -> (PFN) -> BEV scatter for B frames per step.
+
+One :class:`PillarFrontEnd` owns one workspace handle, one set of preallocated output tensors and (optionally)
+one CUDA graph of the whole step, for one GPU and one stream.  Frames are independent, so multi-GPU use is
+"one PillarFrontEnd per rank, frames sharded across ranks, no collective" (see sharding.py).
+
+Per step (all on the current stream, no host synchronisation):
+
+    pf_voxelize_decorate(points, frame_offsets) -> voxels, coors, num, voxel_num, features   (7 kernels)
+    pillar features (B*max_voxels, C) = pfn(features)  or a caller-supplied tensor            (not on the path)
+    pf_scatter_from_map(pillar features)              -> canvas (B, C, nx, ny)                (1 kernel)
+
+The voxeliser's own cell grid doubles as the cell -> pillar map of the scatter, so coordinates are never
+re-indexed and the canvas is written exactly once.
+"""
+from __future__ import annotations
+
+import numpy as np
+import torch
+
+from . import _lib
+from .config import derive_grid
+from .pillar_ops import decorate_constants
+
+
+class PillarFrontEnd:
+    N_KERNELS_VOXELIZE = 7   # quantize, creator_count, assign, tile_rank, column_scan, slot, gather(+decorate)
+    N_KERNELS_SCATTER = 1    # canvas_fill
+
+    def __init__(self, config, max_batch, max_points_per_frame, device=0, n_channels=64, want_voxels=True,
+                 compact=False):
+        if not torch.cuda.is_available():
+            raise _lib.PillarFrontError("no CUDA device: the pillar front end has no CPU fallback")
+        cfg = dict(config)
+        self.geometry = derive_grid(cfg)
+        g = self.geometry
+        self.device = torch.device("cuda", int(device))
+        self.B = int(max_batch)
+        self.max_points_per_frame = int(max_points_per_frame)
+        self.max_voxels = int(cfg["max_voxels"])
+        self.P = int(cfg["max_num_points"])
+        self.F = int(cfg.get("num_point_features", 4))
+        self.C = int(n_channels)
+        self.nx, self.ny, self.nz = (int(x) for x in g.grid_size)
+        if self.nz != 1:
+            raise _lib.PillarFrontError("PillarFrontEnd needs nz == 1 (pillars); use VoxelGenerator + PointPillarsScatter")
+        self.compact = bool(compact)
+        self.consts = decorate_constants(cfg["voxel_size"], g.offset)
+        self.handle = _lib.Handle(g, self.max_voxels, self.P, self.F, self.B, self.max_points_per_frame,
+                                  self.device.index)
+        rows = self.B * self.max_voxels
+        dev = self.device
+        self.voxels = torch.empty((rows, self.P, self.F), dtype=torch.float32, device=dev) if want_voxels else None
+        self.coors = torch.empty((rows, 4), dtype=torch.int32, device=dev)
+        self.num_points = torch.empty((rows,), dtype=torch.int32, device=dev)
+        self.voxel_num = torch.zeros((self.B,), dtype=torch.int32, device=dev)
+        self.features = torch.empty((rows, self.P, self.F + 5), dtype=torch.float32, device=dev)
+        self.canvas = torch.empty((self.B, self.C, self.nx, self.ny), dtype=torch.float32, device=dev)
+        self._graph = None
+        self._g_inputs = None
+
+    # ---- the two stages --------------------------------------------------------------------------
+    def voxelize_decorate(self, points, frame_offsets, n_frames=None, max_frame_points=None):
+        """points: CUDA fp32 (sum N_f, F); frame_offsets: CUDA int32 (n_frames+1,)."""
+        n_frames = self.B if n_frames is None else int(n_frames)
+        mfp = self.max_points_per_frame if max_frame_points is None else int(max_frame_points)
+        h = self.handle
+        vx, vy, xo, yo = self.consts
+        stream = torch.cuda.current_stream(self.device).cuda_stream
+        _lib.check(h.lib.pf_voxelize_decorate(
+            h.ptr, points.data_ptr(), frame_offsets.data_ptr(), n_frames, mfp, int(points.shape[1]),
+            1 if self.compact else 0, 4, vx, vy, xo, yo, 1,
+            self.voxels.data_ptr() if self.voxels is not None else None, self.coors.data_ptr(),
+            self.num_points.data_ptr(), self.voxel_num.data_ptr(), self.features.data_ptr(), stream),
+            "pf_voxelize_decorate")
+
+    def scatter(self, pillar_feats, n_frames=None):
+        """pillar_feats: CUDA fp32 (rows, C) row-major, rows laid out like the voxel outputs."""
+        n_frames = self.B if n_frames is None else int(n_frames)
+        h = self.handle
+        stream = torch.cuda.current_stream(self.device).cuda_stream
+        _lib.check(h.lib.pf_scatter_from_map(h.ptr, pillar_feats.data_ptr(), int(pillar_feats.stride(0)),
+                                             int(pillar_feats.stride(1)), n_frames, 1 if self.compact else 0,
+                                             self.C, self.canvas.data_ptr(), stream), "pf_scatter_from_map")
+        return self.canvas[:n_frames]
+
+    def step(self, points, frame_offsets, pillar_feats=None, pfn=None, n_frames=None, max_frame_points=None):
+        """One pass of the hot path over one batch.  Exactly one of pillar_feats / pfn feeds the scatter."""
+        self.voxelize_decorate(points, frame_offsets, n_frames, max_frame_points)
+        if pfn is not None:
+            pillar_feats = pfn(self.features)
+        if pillar_feats is None:
+            raise ValueError("step needs pillar_feats or pfn")
+        return self.scatter(pillar_feats, n_frames)
+
+    # ---- CUDA graph of a fixed-shape step --------------------------------------------------------
+    def capture(self, points, frame_offsets, pillar_feats):
+        """Capture step() for these (static) tensors; replay() re-runs it on whatever they then contain."""
+        self._g_inputs = (points, frame_offsets, pillar_feats)
+        side = torch.cuda.Stream(self.device)
+        side.wait_stream(torch.cuda.current_stream(self.device))
+        with torch.cuda.stream(side):
+            for _ in range(2):
+                self.step(points, frame_offsets, pillar_feats)
+        torch.cuda.current_stream(self.device).wait_stream(side)
+        torch.cuda.synchronize(self.device)
+        g = torch.cuda.CUDAGraph()
+        with torch.cuda.graph(g):
+            self.step(points, frame_offsets, pillar_feats)
+        self._graph = g
+        return g
+
+    def replay(self):
+        self._graph.replay()
+        return self.canvas
+
+    # ---- host-side views -------------------------------------------------------------------------
+    def frame_outputs(self, f, counts=None):
+        """Slices of frame f in the slab layout (synchronises to read voxel_num unless counts is given)."""
+        if self.compact:
+            raise ValueError("frame_outputs is for the slab layout")
+        counts = self.voxel_num.cpu().numpy() if counts is None else counts
+        v = int(counts[f])
+        lo = f * self.max_voxels
+        sl = slice(lo, lo + v)
+        return (self.voxels[sl] if self.voxels is not None else None, self.coors[sl], self.num_points[sl],
+                self.features[sl])
+
+    def bytes_algorithmic(self, n_points_total, voxel_counts):
+        """API-visible bytes of one step: each tensor once, scratch excluded."""
+        v = int(np.sum(voxel_counts))
+        b = len(voxel_counts)
+        P, F, C = self.P, self.F, self.C
+        vox = 4 * F * n_points_total + 4 * F * P * v + 12 * v + 4 * v
+        dec = 4 * (F + 5) * P * v
+        scat = 4 * C * v + 12 * v + 4 * C * self.nx * self.ny * b
+        return {"voxelize": vox, "decorate_out": dec, "scatter": scat, "e2e": vox + dec + scat}
+
+    def close(self):
+        self.handle.close()

@@ -1,0 +1,130 @@
+/*
+ * pillarfront.h -- C ABI of libpillarfront.so, the B200 (sm_100a) point-cloud front end.
+ *
+ * This is the drop-in boundary for the reference's voxelise -> pillar decoration -> BEV scatter path
+ * (SURVEY.md §8b).  The reference has no FFI of its own (it is Python + numba); the entry points below are
+ * what a ctypes binding of that path needs, one per reference function:
+ *
+ *   pf_voxelize          <-> framework/voxel_generator.py:28-40, 82-106  (VoxelGenerator.generate,
+ *                            numba points_to_voxels), batched over independent frames
+ *   pf_decorate          <-> networks/pointpillars8_shared.py:32-54      (PointNet.forward, decoration prefix;
+ *                            same code inlined at pointpillars8_export.py:186-199, pointpillars_trt.py:103-116)
+ *   pf_voxelize_decorate <-> the two above fused (the pillar never leaves the SM between them)
+ *   pf_scatter           <-> networks/pointpillars8_shared.py:76-111     (PointPillarsScatter.forward),
+ *                            networks/pointpillars8_export.py:44-51      (Scatter.run, channel-major features),
+ *                            networks/pointpillars8_trt.py:139-205       (Scatter_cuda + its CUDA-C kernel)
+ *   pf_scatter_backward  <-> autograd of the index_put in pointpillars8_shared.py:100 (a gather)
+ *
+ * Conventions
+ *   - plain pointers and sizes only; every pointer named *device* is CUDA device memory on the handle's
+ *     device; `stream` is a cudaStream_t passed as void*; all work is enqueued asynchronously on it and no
+ *     call synchronises, allocates or frees (so every call can be captured into a CUDA graph).
+ *   - every function returns 0 on success, a negative pf_status on bad arguments, or a positive
+ *     cudaError_t; it never throws.  pf_last_error_string() describes the last failure of the calling thread.
+ *   - a handle is bound to one device and is not re-entrant: use one handle per (GPU, stream).
+ *   - all outputs are written exactly once per call; nothing needs pre-zeroing by the caller.
+ */
+#ifndef PILLARFRONT_H_
+#define PILLARFRONT_H_
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define PF_VERSION 100 /* 0.1.0 */
+
+#if defined(__GNUC__)
+#define PF_API __attribute__((visibility("default")))
+#else
+#define PF_API
+#endif
+
+typedef enum pf_status {
+    PF_OK = 0,
+    PF_ERR_INVALID_ARGUMENT = -1,
+    PF_ERR_CAPACITY = -2,      /* n_frames / points per frame / voxels exceed what the handle was created for */
+    PF_ERR_UNSUPPORTED = -3,   /* e.g. max_points > 255, num_features outside 3..16 */
+    PF_ERR_OUT_OF_MEMORY = -4
+} pf_status;
+
+/* Grid geometry + caps: the attributes of the reference's VoxelGenerator (framework/voxel_generator.py:17-22). */
+typedef struct pf_grid_desc {
+    float offset[3];      /* lower corner of cell (0,0,0): VoxelGenerator.offset */
+    float voxel_size[3];  /* VoxelGenerator.voxel_size */
+    int32_t grid[3];      /* (nx, ny, nz): VoxelGenerator.grid_size; cells are C-ordered [x][y][z] */
+    int32_t max_voxels;   /* config['max_voxels'] */
+    int32_t max_points;   /* config['max_num_points'] (P), <= 255 */
+    int32_t num_features; /* floats per point (F), 3..16; config['num_point_features'] */
+} pf_grid_desc;
+
+typedef struct pf_handle pf_handle;
+
+PF_API int pf_version(void);
+PF_API const char *pf_last_error_string(void);
+
+/* Create the per-(GPU,stream) workspace: cell grid, per-point scratch, tile counters, slot lists, cell->row map.
+ * `device` < 0 means the current device. */
+PF_API int pf_create(const pf_grid_desc *desc, int max_frames, int max_points_per_frame, int device,
+              pf_handle **out);
+PF_API int pf_destroy(pf_handle *h);
+PF_API size_t pf_workspace_bytes(const pf_handle *h);
+
+/* Output layouts (both written densely, padding rows zeroed):
+ *   slab    (compact == 0): frame f owns rows [f*max_voxels, f*max_voxels + voxel_num[f]) of every output;
+ *   compact (compact != 0): frames are concatenated, frame f starts at row sum(voxel_num[0..f)), exactly what
+ *                           framework/utils.py:23-48 (merge_second_batch) builds on the host.
+ *   voxels     float [rows][P][F]
+ *   coors      int32 [rows][coors_stride]  (x, y, z[, frame id]) -- coors_stride is 3 or 4; the frame id goes
+ *              in the LAST column like merge_second_batch's pad (framework/utils.py:38-41)
+ *   num_points int32 [rows]
+ *   voxel_num  int32 [n_frames]   voxels produced per frame (device memory)
+ *   features   float [rows][P][F+5] (pf_voxelize_decorate only)
+ *
+ * points        device float [frame_offsets[n_frames]][point_stride] (first F floats of each row are used)
+ * frame_offsets device int32 [n_frames+1], frame f is rows [frame_offsets[f], frame_offsets[f+1])
+ * max_frame_points: host-side upper bound of any frame's size in this call (<= the handle's), sizes the grids.
+ */
+PF_API int pf_voxelize(pf_handle *h, const float *points, const int32_t *frame_offsets, int n_frames,
+                int max_frame_points, int point_stride, int compact, int coors_stride,
+                float *voxels, int32_t *coors, int32_t *num_points, int32_t *voxel_num, void *stream);
+
+/* As pf_voxelize, and additionally writes the decorated pillar features; `voxels` may be NULL when only the
+ * features are wanted.  vx, vy, x_off, y_off as PointNet.__init__ forms them (pointpillars8_shared.py:16-19).
+ * keep_cell_map != 0 leaves the handle's cell->voxel map populated so that a following
+ * pf_scatter_from_map can fill the canvas without re-indexing the coordinates (nz must be 1). */
+PF_API int pf_voxelize_decorate(pf_handle *h, const float *points, const int32_t *frame_offsets, int n_frames,
+                         int max_frame_points, int point_stride, int compact, int coors_stride,
+                         float vx, float vy, float x_off, float y_off, int keep_cell_map,
+                         float *voxels, int32_t *coors, int32_t *num_points, int32_t *voxel_num,
+                         float *features, void *stream);
+
+/* Stand-alone decoration of already voxelised pillars (host-known row count). */
+PF_API int pf_decorate(const float *voxels, const int32_t *num_points, const int32_t *coors, int coors_stride,
+                int64_t n_voxels, int max_points, int num_features,
+                float vx, float vy, float x_off, float y_off, float *features, void *stream);
+
+/* BEV scatter.  canvas float [batch][n_ch][nx][ny] is written completely (zeros where no pillar).
+ * feats: element (v, c) at feats[v*feat_stride_v + c*feat_stride_c]  ((V,C) row-major: C,1; (C,V): 1,V).
+ * coors rows (x, y, z[, batch id]); rows with batch id / x / y out of range are ignored; on duplicate cells the
+ * highest row wins (the sequential index_put behaviour). */
+PF_API int pf_scatter(pf_handle *h, const float *feats, int64_t feat_stride_v, int64_t feat_stride_c,
+               const int32_t *coors, int coors_stride, int64_t n_voxels, int batch, int n_ch,
+               float *canvas, void *stream);
+
+/* Fill the canvas from the cell map left by pf_voxelize_decorate(keep_cell_map=1): feature row of voxel v of
+ * frame f is row_base(f) + v with row_base = f*max_voxels (slab) or the running sum of voxel_num (compact). */
+PF_API int pf_scatter_from_map(pf_handle *h, const float *feats, int64_t feat_stride_v, int64_t feat_stride_c,
+                        int n_frames, int compact, int n_ch, float *canvas, void *stream);
+
+/* grad_feats (v, c) = grad_canvas[b][c][x][y]; same stride convention as pf_scatter. */
+PF_API int pf_scatter_backward(const float *grad_canvas, const int32_t *coors, int coors_stride, int64_t n_voxels,
+                        int batch, int n_ch, int nx, int ny, float *grad_feats, int64_t feat_stride_v,
+                        int64_t feat_stride_c, void *stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* PILLARFRONT_H_ */

@@ -1,0 +1,186 @@
+"""GPU parity tests: the CUDA path, called through the C ABI (ctypes), against the oracle and the reference's
+golden vectors.  Integer / index / copy work is bit-exact; the fp32 decoration is held to
+1e-6 * max(1, |xyz|max of the pillar)."""
+import numpy as np
+import pytest
+
+from oracle import oracle
+from tests import util
+from tests.util import cfgmod, synth
+
+pytestmark = pytest.mark.gpu
+torch = pytest.importorskip("torch")
+
+
+@pytest.fixture(scope="module")
+def pfm(pf):
+    assert torch.cuda.is_available()
+    return pf
+
+
+def _np(t):
+    return t.detach().cpu().numpy()
+
+
+# ------------------------------------------------------------------------------------------------ voxelise
+@pytest.mark.parametrize("gkey", util.GRID_KEYS)
+def test_voxelize_small_golden(pfm, gkey):
+    """Every small fixture of one grid through ONE generator instance (also exercises the grid self-reset)."""
+    by_caps = {}
+    for name in util.SMALL_NAMES:
+        g = util.load_small(gkey, name)
+        by_caps.setdefault((int(g["max_voxels"]), int(g["max_points"])), []).append((name, g))
+    for (mv, mp), cases in by_caps.items():
+        cfg = cfgmod.builtin_config(gkey)
+        cfg["max_voxels"], cfg["max_num_points"] = mv, mp
+        vg = pfm.VoxelGenerator(cfg)
+        for rep in range(2):
+            for name, g in cases:
+                got = vg.generate(g["points"])
+                util.assert_vox_equal(got, (g["voxels"], g["coors"], g["num"]), f"{gkey}/{name} rep{rep}")
+        vg.close()
+
+
+@pytest.mark.parametrize("gkey", util.GRID_KEYS)
+@pytest.mark.parametrize("kind", ["S1", "S2", "S3", "S4"])
+def test_voxelize_full_size(pfm, gkey, kind):
+    cfg, geom, pts, h = util.full_frame(gkey, kind)
+    vg = pfm.VoxelGenerator_trt(cfg)
+    v, c, n, vn = vg.generate(pts)
+    want = oracle.generate(geom, pts, cfg["max_voxels"], cfg["max_num_points"])
+    assert vn == len(want[2])
+    util.assert_vox_equal((v, c, n), want, f"{gkey}/{kind}")
+    if util.sha(pts) == h["points_sha"]:      # same synthetic bits as in the build container -> reference hashes
+        assert util.sha(v) == h["voxels_sha"] and util.sha(c) == h["coors_sha"] and util.sha(n) == h["num_sha"]
+    # device in -> device out, same bits
+    dv, dc, dn, _ = vg.generate(torch.from_numpy(pts).cuda())
+    assert dv.is_cuda and np.array_equal(_np(dv).view(np.uint32), v.view(np.uint32))
+    assert np.array_equal(_np(dc), c) and np.array_equal(_np(dn), n)
+    vg.close()
+
+
+def test_voxelize_feature_counts_and_strides(pfm):
+    """F = 3, 5, 7 use the generic (non-float4) load path."""
+    cfg = cfgmod.builtin_config("20cm")
+    cfg["max_voxels"] = 400
+    geom = cfgmod.derive_grid(cfg)
+    base = synth.make_frame("S1", geom, 5000, 77, 600)
+    rng = np.random.default_rng(5)
+    for f in (3, 5, 7):
+        pts = np.ascontiguousarray(np.concatenate([base[:, :3], rng.random((5000, f - 3), dtype=np.float32)], axis=1))
+        vg = pfm.VoxelGenerator(cfg)
+        util.assert_vox_equal(vg.generate(pts), oracle.generate(geom, pts, 400, 15), f"F={f}")
+        vg.close()
+
+
+def test_voxelize_batch_collated(pfm):
+    """generate_batch == merge_second_batch of per-frame results (frame id in the LAST coors column)."""
+    cfg = cfgmod.builtin_config("16cm")
+    cfg["max_voxels"] = 900
+    geom = cfgmod.derive_grid(cfg)
+    frames = [synth.make_frame(k, geom, n, 300 + i, 700) for i, (k, n) in
+              enumerate([("S1", 9000), ("S3", 2500), ("S2", 4096), ("S4", 3000), ("S1", 1)])]
+    frames.insert(2, np.zeros((0, 4), np.float32))
+    vg = pfm.VoxelGenerator(cfg)
+    out = vg.generate_batch(frames, device_outputs=False)
+    refs = [oracle.generate(geom, f, 900, 15) for f in frames]
+    assert out["voxel_num"].tolist() == [len(r[2]) for r in refs]
+    want_v = np.concatenate([r[0] for r in refs])
+    want_c = np.concatenate([np.pad(r[1], ((0, 0), (0, 1)), constant_values=i) for i, r in enumerate(refs)])
+    want_n = np.concatenate([r[2] for r in refs])
+    util.assert_vox_equal((out["voxels"], out["coordinates"], out["num_points_per_voxel"]), (want_v, want_c, want_n))
+    vg.close()
+
+
+def test_voxelize_properties_full_size(pfm):
+    """Size-independent properties at BASELINE.json's full frame size (20 cm, 120k points, overflow case)."""
+    cfg, geom, pts, _ = util.full_frame("20cm", "S2")
+    vg = pfm.VoxelGenerator(cfg)
+    v, c, n = vg.generate(pts)
+    # idempotence
+    v2, c2, n2 = vg.generate(pts)
+    util.assert_vox_equal((v2, c2, n2), (v, c, n), "repeat")
+    # coordinates unique and in range; counts in [1, P]; padding rows zero
+    lin = c[:, 0].astype(np.int64) * geom.grid_size[1] + c[:, 1]
+    assert len(np.unique(lin)) == len(lin) and np.all((c >= 0) & (c < geom.grid_size))
+    assert n.min() >= 1 and n.max() <= cfg["max_num_points"]
+    pad = np.arange(cfg["max_num_points"])[None, :] >= n[:, None]
+    assert not v[pad].any()
+    # every stored point lies in its voxel's cell
+    q = np.floor((v[..., :3] - geom.offset) / geom.voxel_size).astype(np.int64)
+    assert np.array_equal(q[~pad], np.repeat(c, n, axis=0))
+    # permuting the points after the cut-off index i* does not change the output (the loop never reaches them)
+    from oracle import spec_parallel
+    cell, _ = spec_parallel.quantize(geom, pts)
+    ins = np.nonzero(cell >= 0)[0]
+    _, first_pos = np.unique(cell[ins], return_index=True)
+    firsts = np.sort(ins[first_pos])
+    assert len(firsts) > cfg["max_voxels"], "S2 must overflow max_voxels"
+    istar = int(firsts[cfg["max_voxels"]])
+    tail = pts[istar + 1:].copy()
+    np.random.default_rng(0).shuffle(tail)
+    pts2 = np.ascontiguousarray(np.concatenate([pts[:istar + 1], tail]))
+    util.assert_vox_equal(vg.generate(pts2), (v, c, n), "tail shuffle")
+    # appending a copy of a stored point right after it puts the copy in the next slot (or drops it when full)
+    k = int(np.argmax(n < cfg["max_num_points"]))
+    src = int(np.nonzero((pts == v[k, n[k] - 1]).all(1))[0][0])
+    pts3 = np.ascontiguousarray(np.insert(pts, src + 1, pts[src], axis=0))
+    v3, c3, n3 = vg.generate(pts3)
+    util.assert_vox_equal((v3, c3, n3), oracle.generate(geom, pts3, cfg["max_voxels"], cfg["max_num_points"]), "dup")
+    vg.close()
+
+
+def test_voxelize_rejects_bad_input(pfm):
+    vg = pfm.VoxelGenerator(cfgmod.builtin_config("20cm"))
+    with pytest.raises(TypeError):
+        vg.generate(np.zeros((4, 4), np.float64))
+    with pytest.raises(ValueError):
+        vg.generate(np.zeros((4,), np.float32))
+    with pytest.raises(ValueError):
+        vg.generate(np.zeros((4, 2), np.float32))
+    v, c, n = vg.generate(np.zeros((0, 4), np.float32))
+    assert v.shape == (0, 15, 4) and c.shape == (0, 3) and n.shape == (0,)
+    vg.close()
+
+
+# ------------------------------------------------------------------------------------------------ decorate
+@pytest.mark.parametrize("gkey", util.GRID_KEYS)
+@pytest.mark.parametrize("name", ["s1", "s2_ring", "s4_edges", "dense_cap", "n5"])
+def test_decorate_matches_reference(pfm, gkey, name):
+    g = util.load_small(gkey, name)
+    cfg = util.small_config(gkey, g)
+    geom = cfgmod.derive_grid(cfg)
+    consts = pfm.decorate_constants(cfg["voxel_size"], geom.offset)
+    assert consts == oracle.decorate_consts(cfg["voxel_size"], geom.offset)
+    got = _np(pfm.decorate(torch.from_numpy(g["voxels"]).cuda(), torch.from_numpy(g["num"]).cuda(),
+                           torch.from_numpy(g["coors"]).cuda(), *consts))
+    tol = oracle.decorate_tolerance(g["voxels"])
+    for want in (g["features"], oracle.decorate(g["voxels"], g["num"], g["coors"], *consts)):
+        both_nan = np.isnan(got) & np.isnan(want)
+        assert got.shape == want.shape
+        assert np.all((np.abs(got.astype(np.float64) - want) <= tol) | both_nan)
+    assert np.array_equal(got[..., :4].view(np.uint32), g["voxels"].view(np.uint32))     # pass-through is exact
+    # the centre-offset columns see identical rounding steps -> bit-exact against the C oracle
+    want = oracle.decorate(g["voxels"], g["num"], g["coors"], *consts)
+    assert np.array_equal(got[..., 7:9], want[..., 7:9])
+
+
+def test_pointnet_module(pfm):
+    """PointNet keeps the reference's state-dict keys and forward result shape."""
+    cfg = cfgmod.builtin_config("20cm")
+    vgcfg = dict(cfg)
+    vg = pfm.VoxelGenerator(vgcfg)
+    net = pfm.PointNet(cfg["num_point_features"], cfg["voxel_size"], vgcfg["detection_offset"]).cuda().eval()
+    assert sorted(net.state_dict()) == sorted(
+        ["pfn_layers.0.weight", "pfn_layers.1.weight", "pfn_layers.1.bias", "pfn_layers.1.running_mean",
+         "pfn_layers.1.running_var", "pfn_layers.1.num_batches_tracked"])
+    pts = synth.make_frame("S1", vg.geometry, 20000, 9, 3000)
+    v, c, n = vg.generate(pts, device_outputs=True)
+    with torch.no_grad():
+        out = net(v, n, c)
+        feats = torch.from_numpy(oracle.decorate(_np(v), _np(n), _np(c), net.vx, net.vy, net.x_offset,
+                                                 net.y_offset)).cuda()
+        want = torch.max(net.pfn_layers(feats.permute(0, 2, 1).contiguous()).permute(0, 2, 1), dim=1)[0]
+    assert out.shape == (len(n), 64)
+    assert torch.allclose(out, want, rtol=1e-4, atol=1e-4)
+    vg.close()

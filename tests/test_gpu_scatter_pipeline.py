@@ -1,0 +1,152 @@
+"""GPU parity tests for the BEV scatter (bit-exact copy work) and the fused batched pipeline."""
+import numpy as np
+import pytest
+
+from oracle import oracle
+from tests import util
+from tests.util import cfgmod, synth
+
+pytestmark = pytest.mark.gpu
+torch = pytest.importorskip("torch")
+
+
+def _np(t):
+    return t.detach().cpu().numpy()
+
+
+@pytest.mark.parametrize("gkey,name", [("20cm", "s1"), ("20cm", "s4_edges"), ("nuscene", "s1"), ("nuscene", "s4_edges")])
+def test_scatter_matches_reference_golden(pf, gkey, name):
+    g = util.load_small(gkey, name)
+    nx, ny = int(g["grid_size"][0]), int(g["grid_size"][1])
+    feats = torch.from_numpy(g["pillar_feats"]).cuda()
+    coors = torch.from_numpy(g["coors"]).cuda()
+    sc = pf.PointPillarsScatter(batch_size=1, output_shape=g["grid_size"], num_input_features=64)
+    for rep in range(2):                                     # second call checks the map put itself back
+        canvas = _np(sc(feats, coors))
+        assert canvas.shape == tuple(g["canvas_shape"])
+        assert util.sha(canvas) == str(g["canvas_sha"]), f"rep {rep}"
+    # channel-major variants
+    cm = pf.Scatter(g["grid_size"], 64).run(feats.t().contiguous(), coors)
+    assert util.sha(_np(cm)) == str(g["canvas_sha"])
+    cm3 = pf.Scatter(g["grid_size"], 64).run(feats.t().contiguous()[None], coors)
+    assert util.sha(_np(cm3)) == str(g["canvas_sha"])
+    pc = pf.Scatter_cuda(g["grid_size"], 64)
+    out = pc.run(feats.t().contiguous(), coors)
+    assert out.data_ptr() == pc.canvas_d.data_ptr() and util.sha(_np(out)) == str(g["canvas_sha"])
+    out = pc.run((2 * feats).t().contiguous()[:, :7], coors[:7])          # persistent canvas is fully rewritten
+    assert np.array_equal(_np(out), oracle.scatter_cmajor(2 * g["pillar_feats"].T[:, :7], g["coors"][:7], nx, ny))
+
+
+def test_scatter_batched_and_backward(pf):
+    """B > 1: per-frame batch-1 rule, frame id in the last coords column; gradient = gather."""
+    cfg = cfgmod.builtin_config("nuscene")
+    geom = cfgmod.derive_grid(cfg)
+    nx, ny = int(geom.grid_size[0]), int(geom.grid_size[1])
+    rng = np.random.default_rng(3)
+    B, C = 3, 64
+    coors, feats = [], []
+    for b, v in enumerate([700, 0, 1300]):
+        cells = rng.choice(nx * ny, size=v, replace=False)
+        coors.append(np.stack([cells // ny, cells % ny, np.zeros(v, np.int64), np.full(v, b)], 1).astype(np.int32))
+        feats.append(rng.standard_normal((v, C)).astype(np.float32))
+    coors, feats = np.concatenate(coors), np.concatenate(feats)
+    want = oracle.scatter(feats, coors, nx, ny, batch=B)
+    sc = pf.PointPillarsScatter(batch_size=B, output_shape=geom.grid_size, num_input_features=C)
+    ft = torch.from_numpy(feats).cuda().requires_grad_(True)
+    canvas = sc(ft, torch.from_numpy(coors).cuda())
+    assert np.array_equal(_np(canvas), want)
+    gc = torch.from_numpy(rng.standard_normal(want.shape).astype(np.float32)).cuda()
+    canvas.backward(gc)
+    assert np.array_equal(_np(ft.grad), oracle.scatter_backward(_np(gc), coors, batch=B))
+    # odd channel count and a plane that is not a multiple of 128 cells -> generic load path / partial warps
+    nx2, ny2 = 37, 52
+    v = 300
+    cells = rng.choice(nx2 * ny2, size=v, replace=False)
+    co = np.stack([cells // ny2, cells % ny2, np.zeros(v, np.int64)], 1).astype(np.int32)
+    fe = rng.standard_normal((v, 6)).astype(np.float32)
+    sc2 = pf.PointPillarsScatter(1, np.array([nx2, ny2, 1]), 6)
+    assert np.array_equal(_np(sc2(torch.from_numpy(fe).cuda(), torch.from_numpy(co).cuda())),
+                          oracle.scatter(fe, co, nx2, ny2))
+    nx3, ny3 = 5, 7          # plane % 4 != 0 -> scalar fall-back kernel
+    co3 = np.array([[0, 0, 0], [4, 6, 0], [2, 3, 0], [2, 3, 0]], np.int32)      # duplicate cell: last row wins
+    fe3 = rng.standard_normal((4, 3)).astype(np.float32)
+    sc3 = pf.PointPillarsScatter(1, np.array([nx3, ny3, 1]), 3)
+    for _ in range(2):
+        assert np.array_equal(_np(sc3(torch.from_numpy(fe3).cuda(), torch.from_numpy(co3).cuda())),
+                              oracle.scatter(fe3, co3, nx3, ny3))
+
+
+@pytest.mark.parametrize("gkey,compact", [("20cm", False), ("20cm", True), ("nuscene", False), ("10cm", True)])
+def test_pipeline_batched(pf, gkey, compact):
+    """voxelise -> decorate -> scatter for a ragged batch in one launch sequence, slab and collated layouts,
+    eagerly and as a replayed CUDA graph."""
+    cfg = cfgmod.builtin_config(gkey)
+    cfg["max_voxels"] = 2500
+    geom = cfgmod.derive_grid(cfg)
+    P, mv = cfg["max_num_points"], cfg["max_voxels"]
+    spec = [("S1", 30000), ("S3", 9000), ("S2", 20032), ("S4", 6000), ("S1", 0), ("S1", 17)]
+    frames = [synth.make_frame(k, geom, max(n, 8), 40 + i, 2000)[:n if k != "S4" else None] for i, (k, n) in enumerate(spec)]
+    frames = [np.ascontiguousarray(f, np.float32) for f in frames]
+    B = len(frames)
+    sizes = [len(f) for f in frames]
+    fe = pf.PillarFrontEnd(cfg, max_batch=B, max_points_per_frame=max(sizes), device=0, compact=compact)
+    dev = fe.device
+    pts = torch.from_numpy(np.concatenate(frames)).to(dev)
+    offs = torch.tensor(np.concatenate([[0], np.cumsum(sizes)]).astype(np.int32), device=dev)
+    pillar = torch.randn((B * mv, 64), device=dev)
+    consts = oracle.decorate_consts(cfg["voxel_size"], geom.offset)
+    refs = [oracle.generate(geom, f, mv, P) for f in frames]
+    counts_want = [len(r[2]) for r in refs]
+    starts = np.concatenate([[0], np.cumsum(counts_want)]) if compact else np.arange(B + 1) * mv
+
+    def check(canvas):
+        counts = _np(fe.voxel_num)
+        assert counts.tolist() == counts_want
+        pil = _np(pillar)
+        for f, (v, c, n) in enumerate(refs):
+            sl = slice(int(starts[f]), int(starts[f]) + len(n))
+            util.assert_vox_equal((_np(fe.voxels[sl]), _np(fe.coors[sl])[:, :3], _np(fe.num_points[sl])), (v, c, n), f"frame {f}")
+            assert np.all(_np(fe.coors[sl])[:, 3] == f)
+            want_f = oracle.decorate(v, n, c, *consts)
+            assert np.all(np.abs(_np(fe.features[sl]) - want_f) <= oracle.decorate_tolerance(v))
+            assert np.array_equal(_np(canvas[f]), oracle.scatter(pil[sl], c, fe.nx, fe.ny)[0]), f"canvas {f}"
+
+    for _ in range(2):
+        check(fe.step(pts, offs, pillar_feats=pillar))
+    fe.capture(pts, offs, pillar)
+    for _ in range(2):
+        fe.canvas.fill_(7.0)
+        fe.features.fill_(7.0)
+        check(fe.replay())
+    fe.close()
+
+
+def test_pipeline_full_size_checksums(pf):
+    """BASELINE.json configs[1] shape (8 frames x 120k points, 20 cm): size-independent checks at full size."""
+    cfg = cfgmod.builtin_config("20cm")
+    geom = cfgmod.derive_grid(cfg)
+    B, n = 8, cfg["frame_points"]
+    kinds = ["S1", "S2", "S3", "S1", "S2", "S3", "S1", "S4"]
+    frames = [synth.make_frame(k, geom, n, 900 + i, synth.S1_CELLS["20cm"])[:n] for i, k in enumerate(kinds)]
+    fe = pf.PillarFrontEnd(cfg, max_batch=B, max_points_per_frame=n, device=0)
+    dev = fe.device
+    pts = torch.from_numpy(np.concatenate(frames)).to(dev)
+    offs = torch.arange(0, (B + 1) * n, n, dtype=torch.int32, device=dev)
+    pillar = torch.randn((B * cfg["max_voxels"], 64), device=dev)
+    canvas = fe.step(pts, offs, pillar_feats=pillar)
+    counts = _np(fe.voxel_num)
+    for f in (0, 1, 7):                                      # three frames against the oracle, bit-exact
+        v, c, nn = oracle.generate(geom, frames[f], cfg["max_voxels"], cfg["max_num_points"])
+        gv, gc, gn, _ = fe.frame_outputs(f, counts)
+        util.assert_vox_equal((_np(gv), _np(gc)[:, :3], _np(gn)), (v, c, nn), f"frame {f}")
+    # canvas: gathering it back at the coordinates returns the pillar features; everything else is zero
+    for f in range(B):
+        gv, gc, gn, _ = fe.frame_outputs(f, counts)
+        rows = pillar[f * cfg["max_voxels"]: f * cfg["max_voxels"] + int(counts[f])]
+        got = canvas[f][:, gc[:, 0].long(), gc[:, 1].long()].t()
+        assert torch.equal(got, rows)
+        assert torch.count_nonzero(canvas[f]).item() == torch.count_nonzero(rows).item()
+    # second run on the same handle gives the same bits (grid put itself back)
+    c1 = canvas.clone()
+    assert torch.equal(fe.step(pts, offs, pillar_feats=pillar), c1)
+    fe.close()

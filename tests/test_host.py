@@ -1,0 +1,92 @@
+"""CPU tests of the host logic: config/geometry, drop-in side effects, the C-ABI library's exports, sharding."""
+import ctypes
+import importlib
+import re
+from pathlib import Path
+
+import numpy as np
+import pytest
+
+from tests import util
+from tests.util import cfgmod
+
+ROOT = Path(__file__).resolve().parents[1]
+
+
+def test_library_exports_every_declared_symbol():
+    """The built .so loads and exports exactly what include/pillarfront.h declares (no compute without a GPU)."""
+    L = importlib.import_module("3d_object_detection_b200._lib")
+    header = (ROOT / "include" / "pillarfront.h").read_text()
+    declared = sorted(set(re.findall(r"PF_API[^;(]*?\b(pf_\w+)\s*\(", header)))
+    assert declared == sorted(L.EXPORTS)
+    lib = L.load()
+    for name in declared:
+        assert hasattr(lib, name), name
+    assert lib.pf_version() == int(re.search(r"#define PF_VERSION (\d+)", header).group(1))
+    # argument validation works without a device: null descriptor -> PF_ERR_INVALID_ARGUMENT + message
+    out = ctypes.c_void_p()
+    assert lib.pf_create(None, 1, 1, 0, ctypes.byref(out)) == -1
+    assert b"null" in lib.pf_last_error_string()
+    assert ctypes.sizeof(L.GridDesc) == 48
+
+
+@pytest.mark.parametrize("gkey", util.GRID_KEYS)
+def test_geometry_and_config_side_effects(pf, gkey):
+    g = util.load_small(gkey, "s1")
+    cfg = cfgmod.builtin_config(gkey)
+    raw_vs = list(cfg["voxel_size"])
+    vg = pf.VoxelGenerator(cfg)                        # constructing needs no GPU
+    for got, key in [(vg.grid_size, "grid_size"), (vg.offset, "offset"), (vg.voxel_size, "voxel_size"),
+                     (vg.detection_range, "detection_range")]:
+        assert got.dtype == g[key].dtype and np.array_equal(got, g[key]), key
+    # F8: the four keys the reference writes back
+    assert cfg["grid_size"] is vg.grid_size and cfg["detection_offset"] is vg.offset
+    assert np.array_equal(cfg["detection_range"], vg.detection_range)
+    assert np.array_equal(cfg["detection_range_diff"], vg.grid_size.astype(np.float32) * vg.voxel_size)
+    assert cfg["voxel_size"] == raw_vs                 # left alone, PointNet reads the Python floats (F13)
+    assert vg.max_voxels == cfg["max_voxels"] and vg.max_num_points == cfg["max_num_points"]
+
+
+def test_nuscene_offset_is_fp32_exact(pf):
+    geom = cfgmod.derive_grid(cfgmod.builtin_config("nuscene"))
+    assert geom.grid_size.tolist() == [512, 480, 1]
+    assert geom.offset[1] == np.float32(-38.399998) and geom.offset.dtype == np.float32
+
+
+def test_load_config_tolerates_trailing_comma(tmp_path):
+    p = tmp_path / "nuscene.json"
+    p.write_text('{"max_voxels": 12000, "voxel_size": [0.16, 0.16, 6,],\n "eval_step": 100,\n}\n')
+    cfg = cfgmod.load_config(p)
+    assert cfg["max_voxels"] == 12000 and cfg["voxel_size"] == [0.16, 0.16, 6]
+    for stem, key in cfgmod.CONFIG_GRID.items():
+        assert key in cfgmod.GRIDS, stem
+
+
+def test_no_cpu_fallback(pf):
+    import torch
+    if torch.cuda.is_available():
+        pytest.skip("GPU present")
+    vg = pf.VoxelGenerator(cfgmod.builtin_config("20cm"))
+    with pytest.raises(pf.PillarFrontError):
+        vg.generate(np.zeros((3, 4), np.float32))
+    with pytest.raises(pf.PillarFrontError):
+        pf.PointPillarsScatter(1, np.array([8, 8, 1]), 4)(torch.zeros(2, 4), torch.zeros(2, 3, dtype=torch.int32))
+    with pytest.raises(pf.PillarFrontError):
+        pf.decorate(torch.zeros(2, 3, 4), torch.ones(2, dtype=torch.int32), torch.zeros(2, 3, dtype=torch.int32), .2, .2, 0., 0.)
+
+
+def test_product_never_imports_oracle():
+    for path in (ROOT / "3d_object_detection_b200").rglob("*.py"):
+        text = path.read_text()
+        assert not re.search(r"^\s*(from|import)\s+oracle\b", text, re.M), path
+
+
+def test_shard_frames(pf):
+    for n in (0, 1, 7, 8, 64):
+        for g in (1, 2, 4, 8):
+            for mode in ("block", "cyclic"):
+                parts = [pf.shard_frames(n, r, g, mode) for r in range(g)]
+                assert sorted(sum(parts, [])) == list(range(n))
+                assert max(map(len, parts)) - min(map(len, parts)) <= 1
+    with pytest.raises(ValueError):
+        pf.shard_frames(4, 2, 2)
