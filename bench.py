@@ -1,0 +1,361 @@
+#!/usr/bin/env python
+"""bench.py -- points/s and frames/s of the point-cloud front end (voxelise -> decorate -> BEV scatter).
+
+    python bench.py [--gpus N] [--steps K] [--warmup W] [--impl b200|reference] [--grid 20cm] [--batch 8]
+
+A "step" is one pass of the hot path over one batch of B synthetic frames per GPU (BASELINE.json configs[1]:
+seven_20cm/eight_20cm, batch 8 x 120k-point frames, 20 cm pillars).  Frames are independent, so N GPUs run
+N replicas on disjoint frames with no collective on the data path (weak scaling).  Rank 0 prints ONE JSON
+line.  `value` is device-resident throughput (inputs in HBM, whole step replayed as one CUDA graph); `e2e`
+goes through the public Python API with host (pinned) points, H2D and D2H inside the timed region;
+`roofline` is the dominant kernel (canvas fill) against the measured HBM copy bandwidth; `cpu_baseline` /
+`--impl reference` time the CPU oracle port of the reference path on the host cores.
+"""
+from __future__ import annotations
+
+import argparse
+import importlib
+import json
+import os
+import sys
+import threading
+import time
+from pathlib import Path
+
+import numpy as np
+
+ROOT = Path(__file__).resolve().parent
+if str(ROOT) not in sys.path:
+    sys.path.insert(0, str(ROOT))
+
+METRIC = "voxelize+decorate+scatter throughput"
+UNIT = "points/s"
+FRAME_KINDS = ["S1", "S2", "S3"]          # clustered / ring (overflows max_voxels) / uniform (overflows)
+
+
+def parse_args():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=50)
+    ap.add_argument("--warmup", type=int, default=5)
+    ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
+    ap.add_argument("--grid", default="20cm", help="20cm | 10cm | 16cm | nuscene or a config stem")
+    ap.add_argument("--batch", type=int, default=0, help="frames per GPU per step (default: 8; 10cm: 32)")
+    ap.add_argument("--cpu-seconds", type=float, default=12.0, help="CPU-baseline sample budget")
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--pipelines", type=int, default=2, help="e2e: independent stream/workspace sets in flight")
+    return ap.parse_args()
+
+
+def dist_env():
+    rank = int(os.environ.get("RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    return rank, world, local
+
+
+def make_batch(pfm, cfg, geom, batch, rank):
+    """B seeded frames for this rank (kinds cycle S1,S2,S3), concatenated, + int32 offsets."""
+    synth = importlib.import_module("3d_object_detection_b200.synth")
+    cfgmod = importlib.import_module("3d_object_detection_b200.config")
+    gkey = cfgmod.CONFIG_GRID.get(cfg["_name"], cfg["_name"])
+    n = cfg["frame_points"]
+    frames = []
+    for b in range(batch):
+        kind = FRAME_KINDS[b % len(FRAME_KINDS)]
+        seed = synth.frame_seed(50 + rank, b)
+        f = synth.make_frame(kind, geom, n, seed, synth.S1_CELLS.get(gkey, 12000))
+        frames.append(np.ascontiguousarray(f[:n], np.float32))
+    sizes = [len(f) for f in frames]
+    offs = np.concatenate([[0], np.cumsum(sizes)]).astype(np.int32)
+    return frames, np.concatenate(frames), offs
+
+
+class ClockSampler(threading.Thread):
+    """Samples SM clock and throttle reasons through NVML while the timed region runs."""
+
+    def __init__(self, index, period=0.05):
+        super().__init__(daemon=True)
+        self.index, self.period = index, period
+        self.samples, self.reasons, self.max_mhz = [], set(), None
+        self._stop_evt = threading.Event()
+        self.ok = False
+        try:
+            import pynvml
+            pynvml.nvmlInit()
+            self.nv = pynvml
+            self.h = pynvml.nvmlDeviceGetHandleByIndex(index)
+            self.max_mhz = pynvml.nvmlDeviceGetMaxClockInfo(self.h, pynvml.NVML_CLOCK_SM)
+            self.ok = True
+        except Exception:
+            pass
+
+    def run(self):
+        if not self.ok:
+            return
+        nv = self.nv
+        names = {nv.nvmlClocksThrottleReasonHwSlowdown: "hw_slowdown",
+                 nv.nvmlClocksThrottleReasonHwThermalSlowdown: "hw_thermal_slowdown",
+                 nv.nvmlClocksThrottleReasonSwThermalSlowdown: "sw_thermal_slowdown",
+                 nv.nvmlClocksThrottleReasonSwPowerCap: "sw_power_cap"}
+        while not self._stop_evt.is_set():
+            try:
+                self.samples.append(nv.nvmlDeviceGetClockInfo(self.h, nv.NVML_CLOCK_SM))
+                r = nv.nvmlDeviceGetCurrentClocksThrottleReasons(self.h)
+                for bit, name in names.items():
+                    if r & bit:
+                        self.reasons.add(name)
+            except Exception:
+                break
+            time.sleep(self.period)
+
+    def stop(self):
+        self._stop_evt.set()
+        self.join(timeout=2)
+        med = float(np.median(self.samples)) if self.samples else None
+        return {"sm_mhz": med, "sm_max_mhz": self.max_mhz, "reasons": sorted(self.reasons),
+                "samples": len(self.samples)}
+
+
+# ---------------------------------------------------------------------------------------------------------
+# CPU arm: the oracle port of the reference path (C, one frame per OpenMP thread) on the host cores
+def cpu_arm(cfg, geom, frames, pts_cat, offs, steps, warmup, budget_s):
+    from oracle import oracle          # bench.py's cpu_baseline / --impl reference legs may run the oracle
+    b = len(frames)
+    cores = os.cpu_count() or 1
+    threads = min(cores, b)
+    fb = oracle.FrontendBatch(geom, cfg["max_voxels"], cfg["max_num_points"], pts_cat.shape[1], b, 64)
+    consts = oracle.decorate_consts(cfg["voxel_size"], geom.offset)
+    pillar = np.random.default_rng(1).standard_normal((b * cfg["max_voxels"], 64)).astype(np.float32)
+    offs64 = offs.astype(np.int64)
+    for _ in range(max(1, min(warmup, 2))):
+        fb.run(pts_cat, offs64, consts, pillar, threads)
+    times = []
+    t_start = time.perf_counter()
+    for i in range(steps):
+        t0 = time.perf_counter()
+        fb.run(pts_cat, offs64, consts, pillar, threads)
+        times.append(time.perf_counter() - t0)
+        if budget_s and time.perf_counter() - t_start > budget_s and i + 1 >= 3:
+            break
+    total = float(np.sum(times))
+    n_pts = int(pts_cat.shape[0]) * len(times)
+    return {"value": n_pts / total, "unit": UNIT, "cores": threads, "kind": "port",
+            "frames_per_s": b * len(times) / total, "ms_per_step": 1e3 * total / len(times),
+            "steps_run": len(times), "host_cores": cores,
+            "sample": f"{len(times)} batches of {b} frames x {len(frames[0])} points ({cfg['_name']} grid), "
+                      f"C oracle port of numba points_to_voxels + decoration + scatter, "
+                      f"one frame per thread on {threads} of {cores} host cores"}
+
+
+def run_reference(args, rank, world):
+    """--impl reference: the reference's CPU implementation of the path (oracle port; the Python/numba reference
+    cannot travel to the GPU box) on the host cores.  Rank 0 only."""
+    if rank != 0:
+        return
+    pfm = importlib.import_module("3d_object_detection_b200")
+    cfg = pfm.builtin_config(args.grid)
+    cfg["_name"] = args.grid
+    geom = pfm.derive_grid(cfg)
+    batch = args.batch or (32 if "10cm" in args.grid else 8)
+    frames, pts_cat, offs = make_batch(pfm, cfg, geom, batch, 0)
+    # bounded: K steps, each one batch; capped so the whole run stays within a few minutes
+    steps = max(1, min(args.steps, 40))
+    frames, pts_cat, offs = tile_for_cpu(frames, os.cpu_count() or 1)     # one frame per host thread
+    r = cpu_arm(cfg, geom, frames, pts_cat, offs, steps, args.warmup, budget_s=120.0)
+    line = {"impl": "reference", "metric": METRIC, "value": r["value"], "unit": UNIT, "n_gpus": args.gpus,
+            "steps": r["steps_run"], "warmup": min(args.warmup, 2), "ms_per_step": r["ms_per_step"],
+            "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32",
+            "data": "synthetic", "frames_per_s": r["frames_per_s"],
+            "config": {"workload": f"{args.grid}: batch {batch} x {cfg['frame_points']}-point synthetic frames "
+                                   f"(S1/S2/S3 mix), voxelize+decorate+scatter", "grid": args.grid,
+                       "batch_per_gpu": batch, "frame_points": cfg["frame_points"]},
+            "cpu_baseline": {k: r[k] for k in ("value", "unit", "cores", "kind", "sample")},
+            "e2e": {"value": r["value"], "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+            "gpu_launches": 0}
+    print(json.dumps(line), flush=True)
+
+
+def tile_for_cpu(frames, cores, cap=32):
+    """Give the CPU arm enough independent frames to occupy its cores (one frame per thread)."""
+    want = min(max(len(frames), cores), cap)
+    tiled = [frames[i % len(frames)] for i in range(want)]
+    sizes = [len(f) for f in tiled]
+    return tiled, np.concatenate(tiled), np.concatenate([[0], np.cumsum(sizes)]).astype(np.int32)
+
+
+# ---------------------------------------------------------------------------------------------------------
+def run_b200(args, rank, world, local):
+    import torch
+    import torch.distributed as dist
+    pfm = importlib.import_module("3d_object_detection_b200")
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py: no CUDA device (the front end has no CPU fallback)")
+    torch.cuda.set_device(local)
+    dev = torch.device("cuda", local)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=dev)
+
+    cfg = pfm.builtin_config(args.grid)
+    cfg["_name"] = args.grid
+    geom = pfm.derive_grid(cfg)
+    B = args.batch or (32 if "10cm" in args.grid else 8)
+    n_pts_frame = cfg["frame_points"]
+    frames, pts_cat, offs = make_batch(pfm, cfg, geom, B, rank)
+    n_points = int(pts_cat.shape[0])
+    K, W = args.steps, max(args.warmup, 3)
+
+    def barrier():
+        torch.cuda.synchronize(dev)
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize(dev)
+
+    # ---------------- device-resident arm: whole step as one CUDA graph ----------------
+    fe = pfm.PillarFrontEnd(cfg, max_batch=B, max_points_per_frame=n_pts_frame, device=local)
+    pts_d = torch.from_numpy(pts_cat).to(dev)
+    offs_d = torch.from_numpy(offs).to(dev)
+    pillar = torch.randn((B * cfg["max_voxels"], 64), device=dev)      # PFN output stand-in (not on the path)
+    fe.capture(pts_d, offs_d, pillar)
+    for _ in range(W):
+        fe.replay()
+    barrier()
+    sampler = ClockSampler(local)
+    sampler.start()
+    ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    ev0.record()
+    for _ in range(K):
+        fe.replay()
+    ev1.record()
+    barrier()
+    t_dev = ev0.elapsed_time(ev1) * 1e-3
+    counts = fe.voxel_num.cpu().numpy()
+    bytes_alg = fe.bytes_algorithmic(n_points, counts)
+
+    # ---------------- per-stage timing (eager, CUDA events on the launch stream) ----------------
+    st = [torch.cuda.Event(enable_timing=True) for _ in range(3 * K)]
+    for _ in range(3):
+        fe.step(pts_d, offs_d, pillar_feats=pillar)
+    torch.cuda.synchronize(dev)
+    for i in range(K):
+        st[3 * i].record()
+        fe.voxelize_decorate(pts_d, offs_d)
+        st[3 * i + 1].record()
+        fe.scatter(pillar)
+        st[3 * i + 2].record()
+    torch.cuda.synchronize(dev)
+    t_vox = float(np.mean([st[3 * i].elapsed_time(st[3 * i + 1]) for i in range(K)])) * 1e-3
+    t_scat = float(np.mean([st[3 * i + 1].elapsed_time(st[3 * i + 2]) for i in range(K)])) * 1e-3
+    clocks = sampler.stop()
+
+    # ---------------- end-to-end arm: public API, pinned host points in, coords/counts out ----------------
+    depth = max(1, args.pipelines)
+    pipes = []
+    for d in range(depth):
+        p_fe = fe if d == 0 else pfm.PillarFrontEnd(cfg, max_batch=B, max_points_per_frame=n_pts_frame, device=local)
+        pipes.append(dict(fe=p_fe, stream=torch.cuda.Stream(dev),
+                          h_pts=torch.from_numpy(pts_cat).pin_memory(), d_pts=torch.empty_like(pts_d),
+                          h_cnt=torch.empty((B,), dtype=torch.int32).pin_memory(),
+                          h_coors=torch.empty((B * cfg["max_voxels"], 4), dtype=torch.int32).pin_memory()))
+    h2d = pts_cat.nbytes
+    d2h = pipes[0]["h_cnt"].numel() * 4 + pipes[0]["h_coors"].numel() * 4
+
+    def e2e_step(i):
+        p = pipes[i % depth]
+        with torch.cuda.stream(p["stream"]):
+            p["d_pts"].copy_(p["h_pts"], non_blocking=True)
+            p["fe"].step(p["d_pts"], offs_d, pillar_feats=pillar)
+            p["h_cnt"].copy_(p["fe"].voxel_num, non_blocking=True)
+            p["h_coors"].copy_(p["fe"].coors, non_blocking=True)
+
+    for i in range(W):
+        e2e_step(i)
+    barrier()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    cur = torch.cuda.current_stream(dev)
+    e0.record(cur)
+    for p in pipes:
+        p["stream"].wait_event(e0)
+    for i in range(K):
+        e2e_step(i)
+    for p in pipes:
+        cur.wait_stream(p["stream"])
+    e1.record(cur)
+    barrier()
+    t_e2e_local = e0.elapsed_time(e1) * 1e-3
+    assert pipes[0]["h_cnt"].numpy().tolist() == counts.tolist()
+
+    # ---------------- reduce over ranks: MAX time, SUM work ----------------
+    sh = importlib.import_module("3d_object_detection_b200.sharding")
+    t_dev = sh.reduce_max_time(t_dev, dev)
+    t_e2e = sh.reduce_max_time(t_e2e_local, dev)
+    tot_pts, tot_frames = sh.reduce_sum([n_points * K, B * K], dev)
+    if world > 1:
+        dist.barrier()
+    return dict(cfg=cfg, geom=geom, frames=frames, B=B, K=K, W=W, t_dev=t_dev, t_e2e=t_e2e, t_vox=t_vox,
+                t_scat=t_scat, counts=counts, bytes_alg=bytes_alg, n_points=n_points, tot_pts=tot_pts,
+                tot_frames=tot_frames, clocks=clocks, h2d=h2d, d2h=d2h, fe=fe, depth=depth, world=world)
+
+
+def peak_hbm_gbs():
+    p = ROOT / "MEASURED_PEAKS.json"
+    if p.exists():
+        try:
+            return float(json.loads(p.read_text())["hbm_gbs"]), "measured (MEASURED_PEAKS.json hbm_gbs, copy read+write)"
+        except Exception:
+            pass
+    return 6650.0, "fallback (B200_PROFILING.md 6.65 TB/s)"
+
+
+def main():
+    args = parse_args()
+    rank, world, local = dist_env()
+    if args.impl == "reference":
+        run_reference(args, rank, world)
+        return
+    r = run_b200(args, rank, world, local)
+    if rank != 0:
+        return
+    cfg, B, K = r["cfg"], r["B"], r["K"]
+    value = r["tot_pts"] / r["t_dev"]
+    e2e_value = r["tot_pts"] / r["t_e2e"]
+    peak, peak_src = peak_hbm_gbs()
+    scat_bytes = r["bytes_alg"]["scatter"]
+    achieved = scat_bytes / r["t_scat"] / 1e9
+    fe = r["fe"]
+    line = {
+        "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": r["world"], "steps": K, "warmup": r["W"],
+        "ms_per_step": 1e3 * r["t_dev"] / K, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+        "dtype": "f32", "data": "synthetic",
+        "frames_per_s": r["tot_frames"] / r["t_dev"],
+        "config": {"workload": f"{args.grid}: batch {B} x {cfg['frame_points']}-point synthetic frames per GPU "
+                               f"(S1/S2/S3 mix), voxelize+decorate+scatter, canvas ({B},64,{fe.nx},{fe.ny}) fp32",
+                   "grid": args.grid, "batch_per_gpu": B, "frame_points": cfg["frame_points"],
+                   "max_voxels": cfg["max_voxels"], "max_num_points": cfg["max_num_points"],
+                   "voxels_per_frame": r["counts"].tolist(), "parallelism": f"frame-sharded x{r['world']}, no collective",
+                   "l2": f"each step writes a {4 * 64 * fe.nx * fe.ny * B / 1e6:.0f} MB canvas (> 126 MB L2), which "
+                         f"evicts the previous step's lines; no separate flush"},
+        "e2e": {"value": e2e_value, "unit": UNIT, "frames_per_s": r["tot_frames"] / r["t_e2e"],
+                "ms_per_step": 1e3 * r["t_e2e"] / K, "h2d_bytes_per_step": r["h2d"], "d2h_bytes_per_step": r["d2h"],
+                "api": "PillarFrontEnd.step on pinned host points; D2H of voxel_num + coordinates; canvas stays "
+                       "on the GPU for the backbone, as in the reference", "pipelines": r["depth"]},
+        "gpu_launches": K * (fe.N_KERNELS_VOXELIZE + fe.N_KERNELS_SCATTER),
+        "clocks": r["clocks"],
+        "stages_ms": {"voxelize_decorate": 1e3 * r["t_vox"], "scatter": 1e3 * r["t_scat"]},
+        "bytes_per_step": r["bytes_alg"],
+        "e2e_hbm_frac": r["bytes_alg"]["e2e"] / (r["t_dev"] / K) / 1e9 / peak,
+        "roofline": {"kernel": "k_canvas_fill (pf_scatter_from_map)", "bound": "hbm", "achieved": achieved,
+                     "peak": peak, "unit": "GB/s", "frac": achieved / peak, "traffic": None,
+                     "peak_source": peak_src, "frac_of_nominal_8TBs": achieved / 8000.0,
+                     "bytes_per_launch": scat_bytes, "ms_per_launch": 1e3 * r["t_scat"]},
+    }
+    if not args.no_cpu_baseline and r["world"] >= 1:
+        cores = os.cpu_count() or 1
+        tiled, pts_c, offs_c = tile_for_cpu(r["frames"], cores)
+        c = cpu_arm(cfg, r["geom"], tiled, pts_c, offs_c, steps=50, warmup=1, budget_s=args.cpu_seconds)
+        line["cpu_baseline"] = {k: c[k] for k in ("value", "unit", "cores", "kind", "sample", "frames_per_s", "host_cores")}
+    print(json.dumps(line), flush=True)
+
+
+if __name__ == "__main__":
+    main()

@@ -108,7 +108,7 @@ def test_pipeline_batched(pf, gkey, compact):
             util.assert_vox_equal((_np(fe.voxels[sl]), _np(fe.coors[sl])[:, :3], _np(fe.num_points[sl])), (v, c, n), f"frame {f}")
             assert np.all(_np(fe.coors[sl])[:, 3] == f)
             want_f = oracle.decorate(v, n, c, *consts)
-            assert np.all(np.abs(_np(fe.features[sl]) - want_f) <= oracle.decorate_tolerance(v))
+            util.assert_features_close(_np(fe.features[sl]), want_f, oracle.decorate_tolerance(v), f"features {f}")
             assert np.array_equal(_np(canvas[f]), oracle.scatter(pil[sl], c, fe.nx, fe.ny)[0]), f"canvas {f}"
 
     for _ in range(2):

@@ -53,3 +53,14 @@ def assert_vox_equal(got, want, what=""):
     # bit-exact incl. NaN payloads: compare raw words
     assert np.array_equal(np.ascontiguousarray(gv).view(np.uint32), np.ascontiguousarray(wv).view(np.uint32)), \
         f"{what}: voxels differ"
+
+
+def assert_features_close(got, want, tol, what=""):
+    """|got - want| <= tol elementwise; NaN payloads (e.g. a NaN intensity) must be NaN on both sides."""
+    got, want = np.asarray(got), np.asarray(want)
+    assert got.shape == want.shape, f"{what}: shape {got.shape} != {want.shape}"
+    gn, wn = np.isnan(got), np.isnan(want)
+    assert np.array_equal(gn, wn), f"{what}: NaN pattern differs"
+    with np.errstate(invalid="ignore"):
+        ok = (np.abs(got.astype(np.float64) - want) <= tol) | gn
+    assert np.all(ok), f"{what}: {np.count_nonzero(~ok)} elements out of tolerance"
