@@ -27,16 +27,27 @@ __global__ void __launch_bounds__(256) k_map_index(const int32_t *__restrict__ c
 // MODE 0: map holds feature rows (-1 = none), put back to -1 after reading.
 // MODE 1: map is the voxeliser's grid (negative = ~voxel id, anything else = no voxel), put back to kEmpty;
 //         feature row = row_base(frame) + voxel id.
-// FEAT4: features are row-major with 16-byte aligned rows -> one float4 load covers 4 channels of a pillar.
+// FEAT4: features are row-major with 16-byte aligned rows -> 16-byte loads of 4 channels of a pillar.
+//
+// A warp first stages the feature rows of its occupied cells in shared memory with ONE round of coalesced
+// loads (the only exposed L2 latency), then streams the 64 channel lines out of shared memory / zeros.
+// (The first version loaded per channel group inside the store loop: 16 dependent L2 round trips per warp,
+// long-scoreboard bound at 3.3 TB/s -- profiles/r1_fill_v1_ncu.md.)
+constexpr int kFillWarps = 8;
+constexpr int kFillStage = 1152;   // floats of staging per warp: 17 occupied cells x 64 channels in one pass
+
 template <int MODE, bool FEAT4>
-__global__ void __launch_bounds__(256) k_canvas_fill(int32_t *__restrict__ map, const float *__restrict__ feats,
-                                                     long long sv, long long sc, const int32_t *__restrict__ vnum,
-                                                     int max_voxels, int compact, int batch, int n_ch, int plane,
-                                                     float *__restrict__ canvas)
+__global__ void __launch_bounds__(kFillWarps * 32) k_canvas_fill(int32_t *__restrict__ map, const float *__restrict__ feats,
+                                                                 long long sv, long long sc,
+                                                                 const int32_t *__restrict__ vnum, int max_voxels,
+                                                                 int compact, int batch, int n_ch, int plane,
+                                                                 float *__restrict__ canvas)
 {
-    const int lane = threadIdx.x & 31;
+    __shared__ float s_stage[kFillWarps][kFillStage];
+    __shared__ int s_rows[kFillWarps][128];
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     const int chunks = (plane + 127) >> 7;
-    const long long wg = (long long)blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
+    const long long wg = (long long)blockIdx.x * kFillWarps + warp;
     if (wg >= (long long)chunks * batch) return;
     const int b = (int)(wg / chunks);
     const int cell0 = (int)(wg % chunks) * 128 + lane * 4;
@@ -47,48 +58,85 @@ __global__ void __launch_bounds__(256) k_canvas_fill(int32_t *__restrict__ map, 
         for (int o = 16; o > 0; o >>= 1) s += __shfl_xor_sync(0xffffffffu, s, o);
         base = s;
     }
-    if (cell0 >= plane) return;   // plane % 4 == 0 is guaranteed by the launcher
-
-    int32_t *mp = map + (size_t)b * plane + cell0;
-    const int4 m = *reinterpret_cast<const int4 *>(mp);
-    long long row[4];
-    if (MODE == 0) {
-        row[0] = m.x, row[1] = m.y, row[2] = m.z, row[3] = m.w;
-        if ((m.x & m.y & m.z & m.w) != -1) *reinterpret_cast<int4 *>(mp) = make_int4(-1, -1, -1, -1);
-    } else {
-        row[0] = m.x < 0 ? base + ~m.x : -1;
-        row[1] = m.y < 0 ? base + ~m.y : -1;
-        row[2] = m.z < 0 ? base + ~m.z : -1;
-        row[3] = m.w < 0 ? base + ~m.w : -1;
-        if (m.x != kEmpty || m.y != kEmpty || m.z != kEmpty || m.w != kEmpty)
-            *reinterpret_cast<int4 *>(mp) = make_int4(kEmpty, kEmpty, kEmpty, kEmpty);
+    const bool in_plane = cell0 < plane;   // plane % 4 == 0 is guaranteed by the launcher
+    int row[4] = {-1, -1, -1, -1};
+    if (in_plane) {
+        int32_t *mp = map + (size_t)b * plane + cell0;
+        const int4 m = *reinterpret_cast<const int4 *>(mp);
+        if (MODE == 0) {
+            row[0] = m.x, row[1] = m.y, row[2] = m.z, row[3] = m.w;
+            if ((m.x & m.y & m.z & m.w) != -1) *reinterpret_cast<int4 *>(mp) = make_int4(-1, -1, -1, -1);
+        } else {
+            row[0] = m.x < 0 ? (int)(base + ~m.x) : -1;
+            row[1] = m.y < 0 ? (int)(base + ~m.y) : -1;
+            row[2] = m.z < 0 ? (int)(base + ~m.z) : -1;
+            row[3] = m.w < 0 ? (int)(base + ~m.w) : -1;
+            if (m.x != kEmpty || m.y != kEmpty || m.z != kEmpty || m.w != kEmpty)
+                *reinterpret_cast<int4 *>(mp) = make_int4(kEmpty, kEmpty, kEmpty, kEmpty);
+        }
     }
+    // slots: occupied cells of the warp, numbered in cell order
+    const int mine = (row[0] >= 0) + (row[1] >= 0) + (row[2] >= 0) + (row[3] >= 0);
+    int incl = mine;
+    for (int o = 1; o < 32; o <<= 1) {
+        const int v = __shfl_up_sync(0xffffffffu, incl, o);
+        if (lane >= o) incl += v;
+    }
+    const int n_occ = __shfl_sync(0xffffffffu, incl, 31);
     float *dst = canvas + (size_t)b * n_ch * plane + cell0;
-    const bool any = row[0] >= 0 || row[1] >= 0 || row[2] >= 0 || row[3] >= 0;
-    if (!any) {
+    if (n_occ == 0) {
+        if (in_plane) {
 #pragma unroll 8
-        for (int c = 0; c < n_ch; ++c) st_cs_f4(dst + (size_t)c * plane, 0.f, 0.f, 0.f, 0.f);
+            for (int c = 0; c < n_ch; ++c) st_cs_f4(dst + (size_t)c * plane, 0.f, 0.f, 0.f, 0.f);
+        }
         return;
     }
-    if (FEAT4) {
-        for (int c = 0; c < n_ch; c += 4) {
-            float4 q[4];
+    int slot[4];
+    {
+        int s = incl - mine;
 #pragma unroll
-            for (int k = 0; k < 4; ++k)
-                q[k] = row[k] >= 0 ? __ldg(reinterpret_cast<const float4 *>(feats + row[k] * sv + c))
-                                   : make_float4(0.f, 0.f, 0.f, 0.f);
-            st_cs_f4(dst + (size_t)(c + 0) * plane, q[0].x, q[1].x, q[2].x, q[3].x);
-            st_cs_f4(dst + (size_t)(c + 1) * plane, q[0].y, q[1].y, q[2].y, q[3].y);
-            st_cs_f4(dst + (size_t)(c + 2) * plane, q[0].z, q[1].z, q[2].z, q[3].z);
-            st_cs_f4(dst + (size_t)(c + 3) * plane, q[0].w, q[1].w, q[2].w, q[3].w);
+        for (int k = 0; k < 4; ++k) {
+            slot[k] = row[k] >= 0 ? s : -1;
+            if (row[k] >= 0) s_rows[warp][s++] = row[k];
         }
-    } else {
-        for (int c = 0; c < n_ch; ++c) {
-            float q[4];
-#pragma unroll
-            for (int k = 0; k < 4; ++k) q[k] = row[k] >= 0 ? __ldg(feats + row[k] * sv + c * sc) : 0.f;
-            st_cs_f4(dst + (size_t)c * plane, q[0], q[1], q[2], q[3]);
+    }
+    __syncwarp();
+    float *stage = s_stage[warp];
+    int cpp = ((kFillStage / n_occ) - 1) & ~3;   // channels per pass; row stride cpp+1 keeps reads conflict-free
+    if (cpp > n_ch) cpp = n_ch;
+    const int stride = cpp + 1;
+    for (int c0 = 0; c0 < n_ch; c0 += cpp) {
+        const int nc = (n_ch - c0) < cpp ? (n_ch - c0) : cpp;
+        if (FEAT4) {
+            const int q_per = nc >> 2;
+            for (int e = lane; e < n_occ * q_per; e += 32) {
+                const int s = e / q_per, q = e - s * q_per;
+                const float4 v = __ldg(reinterpret_cast<const float4 *>(feats + (long long)s_rows[warp][s] * sv + c0) + q);
+                float *d = stage + s * stride + 4 * q;
+                d[0] = v.x, d[1] = v.y, d[2] = v.z, d[3] = v.w;
+            }
+        } else {
+            for (int e = lane; e < n_occ * nc; e += 32) {
+                const int s = e / nc, cc = e - s * nc;
+                stage[s * stride + cc] = __ldg(feats + (long long)s_rows[warp][s] * sv + (long long)(c0 + cc) * sc);
+            }
         }
+        __syncwarp();
+        if (in_plane) {
+            const float *p0 = stage + (slot[0] >= 0 ? slot[0] : 0) * stride;
+            const float *p1 = stage + (slot[1] >= 0 ? slot[1] : 0) * stride;
+            const float *p2 = stage + (slot[2] >= 0 ? slot[2] : 0) * stride;
+            const float *p3 = stage + (slot[3] >= 0 ? slot[3] : 0) * stride;
+#pragma unroll 4
+            for (int cc = 0; cc < nc; ++cc) {
+                const float a0 = slot[0] >= 0 ? p0[cc] : 0.f;
+                const float a1 = slot[1] >= 0 ? p1[cc] : 0.f;
+                const float a2 = slot[2] >= 0 ? p2[cc] : 0.f;
+                const float a3 = slot[3] >= 0 ? p3[cc] : 0.f;
+                st_cs_f4(dst + (size_t)(c0 + cc) * plane, a0, a1, a2, a3);
+            }
+        }
+        __syncwarp();
     }
 }
 
@@ -160,13 +208,13 @@ static cudaError_t run_fill(int32_t *map, const float *feats, int64_t sv, int64_
         return cudaGetLastError();
     }
     const long long warps = (long long)((plane + 127) / 128) * batch;
-    const unsigned blocks = (unsigned)((warps + 7) / 8);
+    const unsigned blocks = (unsigned)((warps + kFillWarps - 1) / kFillWarps);
     const bool feat4 = (sc == 1) && (sv % 4 == 0) && (n_ch % 4 == 0) && ((reinterpret_cast<uintptr_t>(feats) & 15) == 0);
     if (feat4)
-        k_canvas_fill<MODE, true><<<blocks, 256, 0, stream>>>(map, feats, sv, sc, vnum, max_voxels, compact, batch, n_ch,
+        k_canvas_fill<MODE, true><<<blocks, kFillWarps * 32, 0, stream>>>(map, feats, sv, sc, vnum, max_voxels, compact, batch, n_ch,
                                                               plane, canvas);
     else
-        k_canvas_fill<MODE, false><<<blocks, 256, 0, stream>>>(map, feats, sv, sc, vnum, max_voxels, compact, batch, n_ch,
+        k_canvas_fill<MODE, false><<<blocks, kFillWarps * 32, 0, stream>>>(map, feats, sv, sc, vnum, max_voxels, compact, batch, n_ch,
                                                                plane, canvas);
     return cudaGetLastError();
 }

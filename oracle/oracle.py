@@ -127,8 +127,10 @@ def decorate_f64(voxels, num, coors, vx, vy, x_off, y_off):
 def decorate_tolerance(voxels):
     """Per-pillar absolute tolerance of the decoration parity check: 1e-6 relative to the
     operand magnitude, i.e. 1e-6 * max(1, max |xyz| in the pillar), shape (V,1,1)."""
-    mag = np.abs(np.asarray(voxels)[:, :, :3]).reshape(len(voxels), -1)
-    mag = mag.max(axis=1) if mag.shape[1] else np.zeros(len(voxels))
+    voxels = np.asarray(voxels)
+    if len(voxels) == 0:
+        return np.zeros((0, 1, 1), np.float32)
+    mag = np.abs(voxels[:, :, :3]).reshape(len(voxels), -1).max(axis=1)
     return (1e-6 * np.maximum(1.0, mag)).reshape(-1, 1, 1)
 
 
