@@ -105,6 +105,8 @@ int pf_create(const pf_grid_desc *d, int max_frames, int max_points_per_frame, i
     p.npts_cap = (int)align_up((size_t)max_points_per_frame, pf::kTile);
     p.tiles_cap = p.npts_cap / pf::kTile;
     p.vcols = (int)align_up((size_t)d->max_voxels, 16);
+    p.ny_m = (unsigned)((1ull << 32) / (unsigned)p.ny);   // ny, nz == 1 are short-cut in div_small
+    p.nz_m = (unsigned)((1ull << 32) / (unsigned)p.nz);
     if ((size_t)p.vcols > 200 * 1024) { delete h; return fail(PF_ERR_UNSUPPORTED, "pf_create: max_voxels %d too large for the tile table", d->max_voxels); }
 
     const size_t B = (size_t)max_frames;

@@ -27,6 +27,7 @@ struct Params {
     int npts_cap;     // per-frame stride of the per-point scratch arrays (multiple of kTile)
     int tiles_cap;    // npts_cap / kTile
     int vcols;        // row stride of the count matrix (max_voxels rounded up to 16)
+    unsigned ny_m, nz_m;   // floor(2^32 / ny), floor(2^32 / nz): magic multipliers of div_small()
 };
 
 // Device scratch owned by a handle.  Nothing here is API-visible; none of it counts as algorithmic bytes.
@@ -61,8 +62,29 @@ struct VoxelizeArgs {
     float *features;
 };
 
+// arguments of the per-voxel gather + decoration kernels (pf_voxelize.cu generic, pf_gather.cu F = 4)
+struct GatherArgs {
+    const float *points;             // FROM_POINTS
+    const int32_t *frame_offsets;    // FROM_POINTS
+    int point_stride;
+    int compact;
+    int coors_stride;
+    const float *voxels_in;          // !FROM_POINTS
+    const int32_t *num_in;           // !FROM_POINTS
+    const int32_t *coors_in;         // !FROM_POINTS
+    long long n_voxels;              // !FROM_POINTS
+    float vx, vy, x_off, y_off;
+    float *voxels;                   // may be null
+    int32_t *coors;                  // may be null
+    int32_t *num_points;             // may be null
+    float *features;                 // may be null
+};
+
 // launchers (pf_voxelize.cu / pf_scatter.cu); all asynchronous on `stream`, return the launch error.
 cudaError_t launch_fill_i32(int32_t *dst, int32_t value, size_t n, cudaStream_t stream);
+// F = 4 fast path of the gather/decorate kernel; returns cudaErrorNotSupported when the shape does not qualify
+cudaError_t launch_gather4(const Params &p, const Work &w, const GatherArgs &a, int n_frames, bool from_points,
+                           cudaStream_t stream);
 cudaError_t launch_voxelize(const Params &p, const Work &w, const VoxelizeArgs &a, cudaStream_t stream);
 cudaError_t launch_decorate(const float *voxels, const int32_t *num, const int32_t *coors, int coors_stride,
                             int64_t n_voxels, int P, int F, float vx, float vy, float x_off, float y_off,
@@ -91,6 +113,15 @@ __device__ __forceinline__ int cell_of_point(float x, float y, float z, const Pa
                     (qz < (float)p.nz);
     if (!in) return -1;
     return ((int)qx * p.ny + (int)qy) * p.nz + (int)qz;
+}
+
+// n / d for 0 <= n < 2^31, d >= 1, m = floor(2^32 / d): the estimate is at most one short, fixed by one compare.
+__device__ __forceinline__ int div_small(int n, int d, unsigned m)
+{
+    if (d == 1) return n;
+    int q = (int)__umulhi((unsigned)n, m);
+    if (n - q * d >= d) ++q;
+    return q;
 }
 
 __device__ __forceinline__ unsigned lanemask_lt()

@@ -320,22 +320,6 @@ __global__ void __launch_bounds__(256) k_slot(Params p, Work w, const int32_t *_
 // byte -- padding zeros included -- is written exactly once and fully coalesced.
 //   FROM_POINTS = true : rows come from the point cloud through slotidx (fused voxelise path)
 //   FROM_POINTS = false: rows come from an existing voxels tensor (stand-alone pf_decorate)
-struct GatherArgs {
-    const float *points;             // FROM_POINTS
-    const int32_t *frame_offsets;    // FROM_POINTS
-    int point_stride;
-    int compact;
-    int coors_stride;
-    const float *voxels_in;          // !FROM_POINTS
-    const int32_t *num_in;           // !FROM_POINTS
-    const int32_t *coors_in;         // !FROM_POINTS
-    long long n_voxels;              // !FROM_POINTS
-    float vx, vy, x_off, y_off;
-    float *voxels;                   // may be null
-    int32_t *coors;                  // may be null
-    int32_t *num_points;             // may be null
-    float *features;                 // may be null
-};
 
 __device__ __forceinline__ void copy_out(float *__restrict__ gdst, const float *ssrc, int count, int phase)
 {
@@ -533,8 +517,10 @@ cudaError_t launch_voxelize(const Params &p, const Work &w, const VoxelizeArgs &
     ga.compact = a.compact, ga.coors_stride = a.coors_stride;
     ga.vx = a.vx, ga.vy = a.vy, ga.x_off = a.x_off, ga.y_off = a.y_off;
     ga.voxels = a.voxels, ga.coors = a.coors, ga.num_points = a.num_points, ga.features = a.features;
-    cudaError_t e = dispatch_gather<true>(p, w, ga, dim3((p.max_voxels + 15) / 16, B), dim3((p.max_voxels + 7) / 8, B),
-                                          vec4, stream);
+    cudaError_t e = vec4 ? launch_gather4(p, w, ga, B, true, stream) : cudaErrorNotSupported;
+    if (e == cudaErrorNotSupported)   // generic F / stride / alignment
+        e = dispatch_gather<true>(p, w, ga, dim3((p.max_voxels + 15) / 16, B), dim3((p.max_voxels + 7) / 8, B), vec4,
+                                  stream);
     if (e != cudaSuccess) return e;
     return cudaGetLastError();
 }
@@ -552,6 +538,8 @@ cudaError_t launch_decorate(const float *voxels, const int32_t *num, const int32
     ga.n_voxels = n_voxels;
     ga.vx = vx, ga.vy = vy, ga.x_off = x_off, ga.y_off = y_off;
     ga.features = features;
+    const cudaError_t e4 = launch_gather4(p, w, ga, 1, false, stream);
+    if (e4 != cudaErrorNotSupported) return e4;
     const unsigned b16 = (unsigned)((n_voxels + 15) / 16), b32 = (unsigned)((n_voxels + 7) / 8);
     return dispatch_gather<false>(p, w, ga, dim3(b16, 1), dim3(b32, 1), false, stream);
 }
