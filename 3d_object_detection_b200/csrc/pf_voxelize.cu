@@ -3,7 +3,7 @@
 //
 // Order-free definition implemented here (checked on the CPU by oracle/spec_parallel.py):
 //   first[c]  = lowest index of an inside point in cell c                       (k_quantize, atomicMin)
-//   creator i = first[cell_i] == i ; voxel id = exclusive scan of creator flags  (k_creator_count, k_assign)
+//   creator i = first[cell_i] == i ; voxel id = exclusive scan of creator flags  (k_assign, single pass)
 //   i*        = the creator whose id equals max_voxels (the loop's `break`), else N
 //   slot of i = number of earlier points of the same voxel, from a (tile x voxel) count matrix with a
 //               saturating column scan                                           (k_tile_rank, k_column_scan)
@@ -33,63 +33,78 @@ cudaError_t launch_fill_i32(int32_t *dst, int32_t value, size_t n, cudaStream_t 
 }
 
 // ---------------------------------------------------------------------------------------------------------
-// K1: quantise + range filter + first index per cell.  One thread per point, float4 loads when the point
-// row is 16 bytes.  Writes cellid[i]; atomicMin(grid[cell], i).
+// K1: quantise + range filter + first index per cell.  A thread owns kQPer points, 256 apart (independent
+// load / probe / atomic chains).  float4 loads when the point row is 16 bytes.  Writes cellid[i];
+// atomicMin(grid[cell], i).
+//
+// The L2 serialises atomics per address, a pillar next to the sensor collects thousands of points, and with
+// ~1.2 M points in flight they would all hit the same word at once (nuScenes: 48 us for 2.8 M points).  So the
+// kernel is launched twice: first over the leading 1/16 of every frame, then over the rest, and every point
+// probes the cell first (an L2 read; a cell only ever decreases, so a stale value can only cause a redundant
+// atomic): in the second launch any busy cell already holds an index from the first range and is left alone.
+constexpr int kQPer = 4;
+
 template <bool VEC4>
 __global__ void __launch_bounds__(256) k_quantize(Params p, Work w, const float *__restrict__ points,
-                                                  const int32_t *__restrict__ frame_offsets, int point_stride)
+                                                  const int32_t *__restrict__ frame_offsets, int point_stride,
+                                                  int lo, int hi)
 {
     const int f = blockIdx.y;
     const int base = frame_offsets[f];
-    const int n = frame_offsets[f + 1] - base;
-    const int i = blockIdx.x * blockDim.x + threadIdx.x;
-    if (i == 0) w.istar[f] = n;   // "no break" default; k_assign lowers it when max_voxels overflows
-    if (i >= n) return;
-    float x, y, z;
-    if (VEC4) {
-        const float4 q = __ldg(reinterpret_cast<const float4 *>(points) + (size_t)(base + i));
-        x = q.x, y = q.y, z = q.z;
-    } else {
-        const float *q = points + (size_t)(base + i) * point_stride;
-        x = __ldg(q), y = __ldg(q + 1), z = __ldg(q + 2);
+    const int n_all = frame_offsets[f + 1] - base;
+    const int n = n_all < hi ? n_all : hi;     // this launch covers [lo, min(n, hi))
+    const int i0 = lo + blockIdx.x * (256 * kQPer) + threadIdx.x;
+    if (lo == 0 && blockIdx.x == 0) {
+        if (threadIdx.x == 0) w.istar[f] = n_all;   // "no break" default; k_assign lowers it on max_voxels overflow
+        for (int t = threadIdx.x; t < p.tiles_cap; t += 256)
+            w.tilecnt[(size_t)f * p.tiles_cap + t] = 0;   // look-back status words of k_assign: "not ready"
     }
-    const int c = cell_of_point(x, y, z, p);
-    w.cellid[(size_t)f * p.npts_cap + i] = c;
-    if (c >= 0) atomicMin(w.grid + (size_t)f * p.cells + c, i);
-}
-
-// ---------------------------------------------------------------------------------------------------------
-// K2: creators per tile.  A point is the creator of its cell's voxel iff it holds the cell's first index.
-__global__ void __launch_bounds__(256) k_creator_count(Params p, Work w, const int32_t *__restrict__ frame_offsets)
-{
-    const int f = blockIdx.y, t = blockIdx.x;
-    const int n = frame_offsets[f + 1] - frame_offsets[f];
-    const int start = t * kTile;
-    if (start >= n) return;
-    const int32_t *cellid = w.cellid + (size_t)f * p.npts_cap;
-    const int32_t *grid = w.grid + (size_t)f * p.cells;
-    int cnt = 0;
+    if (i0 >= n) return;
+    int c[kQPer];
+    float x[kQPer], y[kQPer], z[kQPer];
 #pragma unroll
-    for (int k = 0; k < kTile / 256; ++k) {
-        const int i = start + k * 256 + threadIdx.x;
+    for (int k = 0; k < kQPer; ++k) {
+        const int i = i0 + k * 256;
+        x[k] = y[k] = z[k] = __int_as_float(0x7fc00000);   // NaN: outside
         if (i < n) {
-            const int c = cellid[i];
-            if (c >= 0 && grid[c] == i) ++cnt;
+            if (VEC4) {
+                const float4 q = __ldg(reinterpret_cast<const float4 *>(points) + (size_t)(base + i));
+                x[k] = q.x, y[k] = q.y, z[k] = q.z;
+            } else {
+                const float *q = points + (size_t)(base + i) * point_stride;
+                x[k] = __ldg(q), y[k] = __ldg(q + 1), z[k] = __ldg(q + 2);
+            }
         }
     }
-    __shared__ int s_sum;
-    if (threadIdx.x == 0) s_sum = 0;
-    __syncthreads();
-    for (int o = 16; o > 0; o >>= 1) cnt += __shfl_xor_sync(0xffffffffu, cnt, o);
-    if ((threadIdx.x & 31) == 0 && cnt) atomicAdd(&s_sum, cnt);
-    __syncthreads();
-    if (threadIdx.x == 0) w.tilecnt[(size_t)f * p.tiles_cap + t] = s_sum;
+    int32_t *grid = w.grid + (size_t)f * p.cells;
+    int seen[kQPer];
+#pragma unroll
+    for (int k = 0; k < kQPer; ++k) {
+        const int i = i0 + k * 256;
+        c[k] = cell_of_point(x[k], y[k], z[k], p);
+        if (i < n) w.cellid[(size_t)f * p.npts_cap + i] = c[k];
+        seen[k] = c[k] >= 0 ? __ldcg(grid + c[k]) : -1;
+    }
+#pragma unroll
+    for (int k = 0; k < kQPer; ++k) {
+        const int i = i0 + k * 256;
+        if (seen[k] > i) atomicMin(grid + c[k], i);
+    }
 }
 
 // ---------------------------------------------------------------------------------------------------------
-// K3: voxel ids.  Exclusive scan of the creator flags in point order (tile base = sum of earlier tiles'
-// counts); creators below max_voxels record their cell and overwrite grid[cell] with ~id, the creator
-// whose id equals max_voxels publishes the cut-off index i* (the reference's `break`).
+// K2: voxel ids in ONE pass over the points.  A point is the creator of its cell's voxel iff it holds the
+// cell's first index; the voxel id is the exclusive scan of the creator flags in point order.  Tiles of kTile
+// points scan locally (ballot/shuffle) and chain their totals with a decoupled look-back over the per-tile
+// status words (tilecnt: flag << 30 | count; 1 = tile total, 2 = inclusive prefix; zeroed by k_quantize).
+// Creators below max_voxels record their cell and overwrite grid[cell] with ~id; the creator whose id equals
+// max_voxels publishes the cut-off index i* (the reference's `break`).
+// Look-back waits only on tiles with a lower blockIdx.x of the same frame, which are dispatched earlier.
+__device__ __forceinline__ unsigned ld_status(const int32_t *p)
+{
+    return *reinterpret_cast<const volatile unsigned *>(p);
+}
+
 __global__ void __launch_bounds__(256) k_assign(Params p, Work w, const int32_t *__restrict__ frame_offsets,
                                                 int32_t *__restrict__ voxel_num_out)
 {
@@ -104,24 +119,11 @@ __global__ void __launch_bounds__(256) k_assign(Params p, Work w, const int32_t 
     if (start >= n) return;
     const int32_t *cellid = w.cellid + (size_t)f * p.npts_cap;
     int32_t *grid = w.grid + (size_t)f * p.cells;
+    int32_t *status = w.tilecnt + (size_t)f * p.tiles_cap;
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
 
     __shared__ int s_warp[8];
     __shared__ int s_base;
-    // tile base: sum of the creator counts of the earlier tiles of this frame
-    int part = 0;
-    for (int j = tid; j < t; j += 256) part += w.tilecnt[(size_t)f * p.tiles_cap + j];
-    for (int o = 16; o > 0; o >>= 1) part += __shfl_xor_sync(0xffffffffu, part, o);
-    if (lane == 0) s_warp[warp] = part;
-    __syncthreads();
-    if (tid == 0) {
-        int b = 0;
-        for (int k = 0; k < 8; ++k) b += s_warp[k];
-        s_base = b;
-    }
-    __syncthreads();
-    const int tile_base = s_base;
-    __syncthreads();
 
     // thread owns 8 consecutive points
     constexpr int PER = kTile / 256;
@@ -133,14 +135,16 @@ __global__ void __launch_bounds__(256) k_assign(Params p, Work w, const int32_t 
         cells[0] = a.x, cells[1] = a.y, cells[2] = a.z, cells[3] = a.w;
         cells[4] = b.x, cells[5] = b.y, cells[6] = b.z, cells[7] = b.w;
     }
+    int first[PER];
+#pragma unroll
+    for (int k = 0; k < PER; ++k) first[k] = (i0 + k < n && cells[k] >= 0) ? __ldcg(grid + cells[k]) : -1;
     unsigned flags = 0;
 #pragma unroll
-    for (int k = 0; k < PER; ++k) {
-        const int i = i0 + k;
-        if (i < n && cells[k] >= 0 && grid[cells[k]] == i) flags |= 1u << k;
-    }
+    for (int k = 0; k < PER; ++k)
+        if (first[k] == i0 + k) flags |= 1u << k;
     const int mine = __popc(flags);
     int incl = mine;
+#pragma unroll
     for (int o = 1; o < 32; o <<= 1) {
         const int v = __shfl_up_sync(0xffffffffu, incl, o);
         if (lane >= o) incl += v;
@@ -150,10 +154,42 @@ __global__ void __launch_bounds__(256) k_assign(Params p, Work w, const int32_t 
     int warp_off = 0, block_total = 0;
 #pragma unroll
     for (int k = 0; k < 8; ++k) {
-        const int s = s_warp[k];
-        if (k < warp) warp_off += s;
-        block_total += s;
+        const int sv = s_warp[k];
+        if (k < warp) warp_off += sv;
+        block_total += sv;
     }
+    if (warp == 0) {
+        // publish this tile's total first so that no successor ever waits on our own look-back
+        if (lane == 0)
+            *reinterpret_cast<volatile unsigned *>(status + t) = ((t == 0 ? 2u : 1u) << 30) | (unsigned)block_total;
+        int base = 0;
+        if (t > 0) {
+            int j = t - 1 - lane;   // lane 0 looks at the nearest predecessor
+            bool done = false;
+            while (!done) {
+                unsigned st = 2u << 30;   // "before tile 0": inclusive prefix 0
+                if (j >= 0) {
+                    do { st = ld_status(status + j); } while ((st >> 30) == 0u);
+                }
+                const unsigned inc_mask = __ballot_sync(0xffffffffu, (st >> 30) == 2u);
+                int val = (int)(st & 0x3fffffffu);
+                if (inc_mask) {
+                    const int nearest = __ffs(inc_mask) - 1;
+                    if (lane > nearest) val = 0;
+                    done = true;
+                }
+#pragma unroll
+                for (int o = 16; o > 0; o >>= 1) val += __shfl_xor_sync(0xffffffffu, val, o);
+                base += val;
+                j -= 32;
+            }
+            if (lane == 0) *reinterpret_cast<volatile unsigned *>(status + t) = (2u << 30) | (unsigned)(base + block_total);
+        }
+        if (lane == 0) s_base = base;
+    }
+    __syncthreads();
+    const int tile_base = s_base;
+
     int rank = tile_base + warp_off + incl - mine;
 #pragma unroll
     for (int k = 0; k < PER; ++k) {
@@ -266,7 +302,7 @@ __global__ void __launch_bounds__(128) k_column_scan(Params p, Work w, const int
     uint32_t *m = reinterpret_cast<uint32_t *>(w.cnt + (size_t)f * p.tiles_cap * p.vcols + col);
     const size_t row_words = p.vcols / 4;
     int run[4] = {0, 0, 0, 0};
-    constexpr int U = 8;
+    constexpr int U = 16;
     for (int t0 = 0; t0 < n_tiles; t0 += U) {
         uint32_t v[U];
 #pragma unroll
@@ -299,18 +335,33 @@ __global__ void __launch_bounds__(256) k_slot(Params p, Work w, const int32_t *_
 {
     const int f = blockIdx.y;
     const int n = frame_offsets[f + 1] - frame_offsets[f];
-    const int i = blockIdx.x * blockDim.x + threadIdx.x;
-    if (i >= n) return;
-    if (reset_grid) {
-        const int c = w.cellid[(size_t)f * p.npts_cap + i];
-        if (c >= 0) w.grid[(size_t)f * p.cells + c] = kEmpty;
+    const int i0 = blockIdx.x * (256 * kQPer) + threadIdx.x;
+    if (i0 >= n) return;
+    int vr[kQPer], cnt[kQPer];
+#pragma unroll
+    for (int k = 0; k < kQPer; ++k) {
+        const int i = i0 + k * 256;
+        vr[k] = i < n ? w.vr[(size_t)f * p.npts_cap + i] : -1;
     }
-    const int vr = w.vr[(size_t)f * p.npts_cap + i];
-    if (vr < 0) return;
-    const int v = vr >> 8, r = vr & 0xff;
-    const int t = i / kTile;
-    const int slot = (int)w.cnt[((size_t)f * p.tiles_cap + t) * p.vcols + v] + r;
-    if (slot < p.P) w.slotidx[((size_t)f * p.max_voxels + v) * p.P + slot] = i;
+    if (reset_grid) {
+#pragma unroll
+        for (int k = 0; k < kQPer; ++k) {
+            const int i = i0 + k * 256;
+            const int c = i < n ? w.cellid[(size_t)f * p.npts_cap + i] : -1;
+            if (c >= 0) w.grid[(size_t)f * p.cells + c] = kEmpty;
+        }
+    }
+#pragma unroll
+    for (int k = 0; k < kQPer; ++k) {
+        const int i = i0 + k * 256;
+        cnt[k] = vr[k] >= 0 ? (int)w.cnt[((size_t)f * p.tiles_cap + i / kTile) * p.vcols + (vr[k] >> 8)] : 0;
+    }
+#pragma unroll
+    for (int k = 0; k < kQPer; ++k) {
+        if (vr[k] < 0) continue;
+        const int v = vr[k] >> 8, slot = cnt[k] + (vr[k] & 0xff);
+        if (slot < p.P) w.slotidx[((size_t)f * p.max_voxels + v) * p.P + slot] = i0 + k * 256;
+    }
 }
 
 // ---------------------------------------------------------------------------------------------------------
@@ -498,11 +549,17 @@ cudaError_t launch_voxelize(const Params &p, const Work &w, const VoxelizeArgs &
     if (npts < 1) npts = 1;
     const int tiles = (npts + kTile - 1) / kTile;
     const bool vec4 = (a.point_stride == 4) && (p.F == 4) && ((reinterpret_cast<uintptr_t>(a.points) & 15) == 0);
-    const dim3 g_pts((npts + 255) / 256, B), g_tiles(tiles, B);
-
-    if (vec4) k_quantize<true><<<g_pts, 256, 0, stream>>>(p, w, a.points, a.frame_offsets, a.point_stride);
-    else      k_quantize<false><<<g_pts, 256, 0, stream>>>(p, w, a.points, a.frame_offsets, a.point_stride);
-    k_creator_count<<<g_tiles, 256, 0, stream>>>(p, w, a.frame_offsets);
+    constexpr int kPtsPerCta = 256 * kQPer;
+    const dim3 g_pts((npts + kPtsPerCta - 1) / kPtsPerCta, B), g_tiles(tiles, B);
+    // leading 1/16 of every frame first (see k_quantize); small frames go in one launch
+    const int split = npts >= 32 * kPtsPerCta ? ((npts / 16 + kPtsPerCta - 1) / kPtsPerCta) * kPtsPerCta : npts;
+    for (int pass = 0; pass < 2; ++pass) {
+        const int lo = pass == 0 ? 0 : split, hi = pass == 0 ? split : npts;
+        if (lo >= hi) continue;
+        const dim3 g((hi - lo + kPtsPerCta - 1) / kPtsPerCta, B);
+        if (vec4) k_quantize<true><<<g, 256, 0, stream>>>(p, w, a.points, a.frame_offsets, a.point_stride, lo, hi);
+        else      k_quantize<false><<<g, 256, 0, stream>>>(p, w, a.points, a.frame_offsets, a.point_stride, lo, hi);
+    }
     k_assign<<<g_tiles, 256, 0, stream>>>(p, w, a.frame_offsets, a.voxel_num);
     if ((size_t)p.vcols > 48 * 1024) {
         cudaError_t e = cudaFuncSetAttribute(k_tile_rank, cudaFuncAttributeMaxDynamicSharedMemorySize, p.vcols);

@@ -6,7 +6,7 @@ one CUDA graph of the whole step, for one GPU and one stream.  Frames are indepe
 
 Per step (all on the current stream, no host synchronisation):
 
-    pf_voxelize_decorate(points, frame_offsets) -> voxels, coors, num, voxel_num, features   (7 kernels)
+    pf_voxelize_decorate(points, frame_offsets) -> voxels, coors, num, voxel_num, features   (6-7 kernels)
     pillar features (B*max_voxels, C) = pfn(features)  or a caller-supplied tensor            (not on the path)
     pf_scatter_from_map(pillar features)              -> canvas (B, C, nx, ny)                (1 kernel)
 
@@ -24,8 +24,13 @@ from .pillar_ops import decorate_constants
 
 
 class PillarFrontEnd:
-    N_KERNELS_VOXELIZE = 7   # quantize, creator_count, assign, tile_rank, column_scan, slot, gather(+decorate)
     N_KERNELS_SCATTER = 1    # canvas_fill
+
+    @staticmethod
+    def n_kernels_voxelize(max_frame_points: int) -> int:
+        """Launches of one pf_voxelize_decorate call: quantize (two index ranges once a frame has >= 32768
+        points, csrc/pf_voxelize.cu), assign, tile_rank, column_scan, slot, gather(+decorate)."""
+        return (2 if max_frame_points >= 32 * 1024 else 1) + 5
 
     def __init__(self, config, max_batch, max_points_per_frame, device=0, n_channels=64, want_voxels=True,
                  compact=False):

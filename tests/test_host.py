@@ -90,3 +90,49 @@ def test_shard_frames(pf):
                 assert max(map(len, parts)) - min(map(len, parts)) <= 1
     with pytest.raises(ValueError):
         pf.shard_frames(4, 2, 2)
+
+
+_GLOO_WORKER = r"""
+import importlib, json, os, sys
+sys.path.insert(0, sys.argv[1])
+import torch.distributed as dist
+sh = importlib.import_module("3d_object_detection_b200.sharding")
+dist.init_process_group("gloo")
+r, g = dist.get_rank(), dist.get_world_size()
+mine = sh.shard_frames(13, r, g, "block")
+t = sh.reduce_max_time(0.25 * (r + 1))
+tot = sh.reduce_sum([len(mine), 1000 * len(mine)])
+dist.barrier()
+if r == 0:
+    print(json.dumps({"t": t, "tot": tot, "world": g}))
+dist.destroy_process_group()
+"""
+
+
+def test_sharded_reductions_gloo_world2(tmp_path):
+    """N > 1 path of bench.py on CPU: two gloo ranks shard 13 frames, MAX the time, SUM the work."""
+    import json
+    import subprocess
+    import sys
+    script = tmp_path / "worker.py"
+    script.write_text(_GLOO_WORKER)
+    cmd = [sys.executable, "-m", "torch.distributed.run", "--nnodes=1", "--nproc-per-node=2", "--master-addr", "127.0.0.1",
+           "--master-port", "29731", str(script), str(ROOT)]
+    res = subprocess.run(cmd, capture_output=True, text=True, timeout=240)
+    assert res.returncode == 0, res.stderr[-2000:]
+    line = [ln for ln in res.stdout.splitlines() if ln.startswith("{")][-1]
+    out = json.loads(line)
+    assert out["world"] == 2 and out["t"] == pytest.approx(0.5) and out["tot"] == [13.0, 13000.0]
+
+
+def test_bench_reference_arm_runs_on_cpu():
+    """bench.py --impl reference needs no GPU: one JSON line with the contract's keys."""
+    import json
+    import subprocess
+    import sys
+    res = subprocess.run([sys.executable, str(ROOT / "bench.py"), "--impl", "reference", "--steps", "2", "--warmup", "1"],
+                         capture_output=True, text=True, timeout=600)
+    assert res.returncode == 0, res.stderr[-2000:]
+    line = json.loads([ln for ln in res.stdout.splitlines() if ln.startswith("{")][-1])
+    assert line["impl"] == "reference" and line["unit"] == "points/s" and line["value"] > 0
+    assert line["cpu_baseline"]["kind"] == "port" and line["e2e"]["h2d_bytes_per_step"] == 0

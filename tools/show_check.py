@@ -20,8 +20,11 @@ for g in ["20cm", "nuscene"]:
         d.setdefault(k, {})[r[h.index("Metric Name")]] = float(r[h.index("Metric Value")])
     print(f"-- {g} launch list (ncu, cold, serialised)")
     tot = 0
-    n = len(d) // 2
-    for k, v in sorted(d.items())[n:]:
+    items = sorted(d.items())
+    starts = [i for i, (k, v) in enumerate(items) if "k_quantize" in k[1] and (i == 0 or "k_quantize" not in items[i - 1][0][1])]
+    lo = starts[-2] if len(starts) >= 2 and len(items) - starts[-1] < starts[-1] - starts[-2] else starts[-1]
+    hi = lo + (starts[-1] - starts[-2] if len(starts) >= 2 else len(items) - lo)
+    for k, v in items[lo:hi]:
         tot += v["gpu__time_duration.sum"]
         print(f"  {k[1]:28s} {v['gpu__time_duration.sum']/1e3:8.1f} us  rd {v['dram__bytes_read.sum']/1e6:7.1f} MB  "
               f"wr {v['dram__bytes_write.sum']/1e6:7.1f} MB  inst {v['smsp__inst_executed.sum']/1e6:6.2f} M")
