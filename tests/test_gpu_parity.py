@@ -73,6 +73,49 @@ def test_voxelize_feature_counts_and_strides(pfm):
         vg.close()
 
 
+@pytest.mark.parametrize("name", util.EXTRA_NAMES)
+def test_voxelize_extra_geometries(pfm, name):
+    """True 3-D grids (nz > 1) and F = 3 / 6 point rows against the reference's own outputs."""
+    g, cfg = util.load_extra(name)
+    vg = pfm.VoxelGenerator(cfg)
+    for rep in range(2):
+        util.assert_vox_equal(vg.generate(g["points"]), (g["voxels"], g["coors"], g["num"]), f"{name} rep{rep}")
+    out = vg.generate_batch([g["points"], g["points"][: len(g["points"]) // 3], g["points"]], device_outputs=False)
+    geom = cfgmod.derive_grid(dict(cfg))
+    refs = [oracle.generate(geom, p, cfg["max_voxels"], cfg["max_num_points"])
+            for p in (g["points"], g["points"][: len(g["points"]) // 3], g["points"])]
+    assert out["voxel_num"].tolist() == [len(r[2]) for r in refs]
+    util.assert_vox_equal((out["voxels"], out["coordinates"][:, :3], out["num_points_per_voxel"]),
+                          tuple(np.concatenate([r[k] for r in refs]) for k in range(3)), f"{name} batch")
+    vg.close()
+
+
+def test_voxelize_random_geometries(pfm):
+    """30 seeded random grids / caps / feature counts / cloud sizes (incl. empty, duplicate and boundary points)."""
+    rng = np.random.default_rng(2024)
+    for case in range(30):
+        nx, ny, nz = (int(rng.integers(1, 40)), int(rng.integers(1, 40)), int(rng.integers(1, 5)))
+        vs = np.array([0.5, 0.25, 1.0])
+        lo = np.array([-3.0, 1.0, -2.0])
+        f = int(rng.integers(3, 7))
+        cfg = dict(detection_range=list(lo) + list(lo + vs * [nx, ny, nz]), voxel_size=list(vs),
+                   max_voxels=int(rng.integers(1, 400)), max_num_points=int(rng.integers(1, 40)),
+                   num_point_features=f, batch_size=1, device=0)
+        geom = cfgmod.derive_grid(dict(cfg))
+        n = int(rng.choice([0, 1, 7, 300, 5000, 40000]))
+        span = vs * [nx, ny, nz]
+        pts = (lo - 0.2 * span + rng.random((n, 3)) * 1.4 * span).astype(np.float32)
+        pts = np.ascontiguousarray(np.concatenate([pts, rng.random((n, f - 3), dtype=np.float32)], axis=1))
+        if n > 8:
+            pts[rng.integers(0, n, n // 4)] = pts[rng.integers(0, n, n // 4)]
+            k = rng.integers(0, n, n // 8)
+            pts[k, 1] = (lo[1] + vs[1] * rng.integers(0, ny + 1, len(k))).astype(np.float32)
+        vg = pfm.VoxelGenerator(cfg)
+        want = oracle.generate(geom, pts, cfg["max_voxels"], cfg["max_num_points"])
+        util.assert_vox_equal(vg.generate(pts), want, f"case {case}: grid {(nx, ny, nz)} F={f} n={n} cfg={cfg}")
+        vg.close()
+
+
 def test_voxelize_batch_collated(pfm):
     """generate_batch == merge_second_batch of per-frame results (frame id in the LAST coors column)."""
     cfg = cfgmod.builtin_config("16cm")

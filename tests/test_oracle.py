@@ -110,3 +110,51 @@ def test_micro_cases():
     pts[:, 3] = np.arange(40)
     v, c, n = oracle.generate(geom, pts, 16000, 15)
     assert n.tolist() == [15] and v[0, :, 3].tolist() == list(range(15))
+
+
+@pytest.mark.parametrize("name", util.EXTRA_NAMES)
+def test_oracle_extra_geometries_match_reference(name):
+    """nz > 1 grids and F != 4 point rows, pinned by the reference's own outputs."""
+    g, cfg = util.load_extra(name)
+    geom = cfgmod.derive_grid(cfg)
+    assert np.array_equal(geom.grid_size, g["grid_size"])
+    assert np.array_equal(geom.offset.view(np.uint32), g["offset"].view(np.uint32))
+    want = (g["voxels"], g["coors"], g["num"])
+    util.assert_vox_equal(oracle.generate(geom, g["points"], cfg["max_voxels"], cfg["max_num_points"]), want, name)
+    util.assert_vox_equal(spec_parallel.voxelize_sorted(geom, g["points"], cfg["max_voxels"], cfg["max_num_points"]),
+                          want, f"{name} sorted spec")
+    util.assert_vox_equal(spec_parallel.voxelize_tiled(geom, g["points"], cfg["max_voxels"], cfg["max_num_points"],
+                                                       tile=256), want, f"{name} tiled spec")
+
+
+def test_oracle_vs_parallel_spec_random_geometries():
+    """Property test (hypothesis): on random small grids / caps / clouds the sequential C oracle and the order-free
+    parallel statement agree bit for bit, and the documented invariants hold."""
+    hyp = pytest.importorskip("hypothesis")
+    from hypothesis import given, settings, strategies as st
+
+    @settings(max_examples=60, deadline=None)
+    @given(seed=st.integers(0, 2 ** 31 - 1), nx=st.integers(1, 12), ny=st.integers(1, 12), nz=st.integers(1, 4),
+           max_voxels=st.integers(1, 60), max_points=st.integers(1, 6), n=st.integers(0, 300), f=st.integers(3, 6))
+    def run(seed, nx, ny, nz, max_voxels, max_points, n, f):
+        rng = np.random.default_rng(seed)
+        vs = np.array([0.5, 0.25, 1.0])
+        lo = np.array([-1.0, 2.0, -3.0])
+        cfg = dict(detection_range=list(lo) + list(lo + vs * [nx, ny, nz]), voxel_size=list(vs),
+                   max_voxels=max_voxels, max_num_points=max_points, num_point_features=f)
+        geom = cfgmod.derive_grid(cfg)
+        span = vs * [nx, ny, nz]
+        pts = (lo - 0.2 * span + rng.random((n, 3)) * 1.4 * span).astype(np.float32)
+        pts = np.ascontiguousarray(np.concatenate([pts, rng.random((n, f - 3), dtype=np.float32)], axis=1))
+        if n:   # duplicates and exact cell boundaries
+            pts[rng.integers(0, n, n // 4)] = pts[rng.integers(0, n, n // 4)]
+            k = rng.integers(0, n, n // 8)
+            pts[k, 0] = (lo[0] + vs[0] * rng.integers(0, nx + 1, len(k))).astype(np.float32)
+        v, c, m = oracle.generate(geom, pts, max_voxels, max_points)
+        util.assert_vox_equal(spec_parallel.voxelize_sorted(geom, pts, max_voxels, max_points), (v, c, m), "sorted")
+        util.assert_vox_equal(spec_parallel.voxelize_tiled(geom, pts, max_voxels, max_points, tile=32), (v, c, m), "tiled")
+        assert len(m) <= max_voxels and (len(m) == 0 or (m.min() >= 1 and m.max() <= max_points))
+        assert len(np.unique(c, axis=0)) == len(c)
+        assert np.all((c >= 0) & (c < geom.grid_size))
+
+    run()

@@ -64,3 +64,16 @@ def assert_features_close(got, want, tol, what=""):
     with np.errstate(invalid="ignore"):
         ok = (np.abs(got.astype(np.float64) - want) <= tol) | gn
     assert np.all(ok), f"{what}: {np.count_nonzero(~ok)} elements out of tolerance"
+
+
+EXTRA_NAMES = ["3d_overflow", "3d_fits", "3d_f6", "2d_f3"]
+
+
+def load_extra(name):
+    """Reference outputs for geometries no shipped config uses (nz > 1, F != 4): oracle/make_golden_extra.py."""
+    z = np.load(GOLD / f"extra_{name}.npz")
+    g = {k: z[k] for k in z.files}
+    cfg = dict(detection_range=[float(x) for x in g["detection_range"]], voxel_size=[float(x) for x in g["voxel_size_cfg"]],
+               max_voxels=int(g["max_voxels"]), max_num_points=int(g["max_points"]),
+               num_point_features=int(g["points"].shape[1]), batch_size=1, device=0)
+    return g, cfg

@@ -22,15 +22,15 @@ constexpr int kW = 8, kStage = 1152;
 enum { NOLOAD = 1, NOLDS = 2, NOMAPW = 4, PLAINST = 8, CH16 = 16, SPLIT = 32, SPLIT1 = 64 };
 
 // FLAGS: experiment switches; CPW = channels per warp (64 = whole column, 16 = grid.y splits the channels)
-template <int FLAGS, int CPW, int STAGE = kStage, int MINB = 1>
-__global__ void __launch_bounds__(kW * 32, MINB) k_fill(int32_t *__restrict__ map, const float *__restrict__ feats, int n_ch,
+template <int FLAGS, int CPW, int STAGE = kStage, int MINB = 1, int NW = kW>
+__global__ void __launch_bounds__(NW * 32, MINB) k_fill(int32_t *__restrict__ map, const float *__restrict__ feats, int n_ch,
                                                   int batch, int plane, float *__restrict__ canvas)
 {
-    __shared__ float s_stage[kW][STAGE];
-    __shared__ int s_rows[kW][128];
+    __shared__ float s_stage[NW][STAGE];
+    __shared__ int s_rows[NW][128];
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     const int chunks = (plane + 127) >> 7;
-    const long long wg = (long long)blockIdx.x * kW + warp;
+    const long long wg = (long long)blockIdx.x * NW + warp;
     if (wg >= (long long)chunks * batch) return;
     const int b = (int)(wg / chunks);
     const int cell0 = (int)(wg % chunks) * 128 + lane * 4;
@@ -309,29 +309,16 @@ int main()
     TIME("8 ch per warp (grid.y=8) uniform", (k_fill<NOMAPW, 8><<<dim3(blocks, 8), 256>>>(map_occ, feats, C, B, plane, canvas)));
     TIME("8 ch per warp (grid.y=8) clustered", (k_fill<NOMAPW, 8><<<dim3(blocks, 8), 256>>>(map_clu, feats, C, B, plane, canvas)));
     TIME("32 ch per warp (grid.y=2) uniform", (k_fill<NOMAPW, 32><<<dim3(blocks, 2), 256>>>(map_occ, feats, C, B, plane, canvas)));
-    TIME("v5 split by sector, uniform", (k_fill<SPLIT, 64><<<blocks, 256>>>(map_occ, feats, C, B, plane, canvas)));
-    TIME("v5 split by sector, clustered", (k_fill<SPLIT, 64><<<blocks, 256>>>(map_clu, feats, C, B, plane, canvas)));
-    TIME("v5 split by lane (16 B), uniform", (k_fill<SPLIT1, 64><<<blocks, 256>>>(map_occ, feats, C, B, plane, canvas)));
-    TIME("v5 split by sector, 32 ch per warp, uniform", (k_fill<SPLIT | NOMAPW, 32><<<dim3(blocks, 2), 256>>>(map_occ, feats, C, B, plane, canvas)));
-    TIME("v6 pipe 16ch order0 grid 148*4 uniform", (k_fill6<16, 8, 0><<<148 * 4, 256>>>(map_occ, feats, C, B, plane, canvas)));
-    TIME("v6 pipe 16ch order0 grid 148*4 empty", (k_fill6<16, 8, 0><<<148 * 4, 256>>>(map_empty, feats, C, B, plane, canvas)));
-    TIME("v6 pipe 16ch order0 grid 148*6 uniform", (k_fill6<16, 8, 0><<<148 * 6, 256>>>(map_occ, feats, C, B, plane, canvas)));
-    TIME("v6 pipe 16ch order0 grid 148*8 uniform", (k_fill6<16, 8, 0><<<148 * 8, 256>>>(map_occ, feats, C, B, plane, canvas)));
-    TIME("v6 pipe 16ch order1 grid 148*6 uniform", (k_fill6<16, 8, 1><<<148 * 6, 256>>>(map_occ, feats, C, B, plane, canvas)));
-    TIME("v6 pipe 8ch order0 grid 148*6 uniform", (k_fill6<8, 8, 0><<<148 * 6, 256>>>(map_occ, feats, C, B, plane, canvas)));
-    TIME("v6 pipe 32ch order0 grid 148*6 uniform", (k_fill6<32, 8, 0><<<148 * 6, 256>>>(map_occ, feats, C, B, plane, canvas)));
-    TIME("v6 pipe 64ch order0 grid 148*4 uniform", (k_fill6<64, 8, 0><<<148 * 4, 256>>>(map_occ, feats, C, B, plane, canvas)));
-    TIME("v6 pipe 64ch order0 grid 148*4 empty", (k_fill6<64, 8, 0><<<148 * 4, 256>>>(map_empty, feats, C, B, plane, canvas)));
     TIME("v2 stage 640 minb 6 uniform", (k_fill<0, 64, 640, 6><<<blocks, 256>>>(map_occ, feats, C, B, plane, canvas)));
     TIME("v2 stage 640 minb 8 uniform", (k_fill<0, 64, 640, 8><<<blocks, 256>>>(map_occ, feats, C, B, plane, canvas)));
     TIME("v2 stage 640 minb 8 empty", (k_fill<0, 64, 640, 8><<<blocks, 256>>>(map_empty, feats, C, B, plane, canvas)));
     TIME("v2 stage 640 minb 6 clustered", (k_fill<0, 64, 640, 6><<<blocks, 256>>>(map_clu, feats, C, B, plane, canvas)));
     TIME("v2 stage 640 minb 8, 32ch uniform", (k_fill<NOMAPW, 32, 640, 8><<<dim3(blocks, 2), 256>>>(map_occ, feats, C, B, plane, canvas)));
-    TIME("v4 zero-then-patch, empty", (k_fill4<0, 64><<<blocks, 256>>>(map_empty, feats, C, B, plane, canvas)));
-    TIME("v4 zero-then-patch, uniform", (k_fill4<0, 64><<<blocks, 256>>>(map_occ, feats, C, B, plane, canvas)));
-    TIME("v4 zero-then-patch, clustered", (k_fill4<0, 64><<<blocks, 256>>>(map_clu, feats, C, B, plane, canvas)));
-    TIME("v4 plain st, uniform", (k_fill4<PLAINST, 64><<<blocks, 256>>>(map_occ, feats, C, B, plane, canvas)));
-    TIME("v4 32 ch per warp (grid.y=2), uniform", (k_fill4<NOMAPW, 32><<<dim3(blocks, 2), 256>>>(map_occ, feats, C, B, plane, canvas)));
-    TIME("v4 32 ch per warp (grid.y=2), clustered", (k_fill4<NOMAPW, 32><<<dim3(blocks, 2), 256>>>(map_clu, feats, C, B, plane, canvas)));
+    TIME("v2 4 warps per CTA uniform", (k_fill<0, 64, kStage, 1, 4><<<blocks * 2, 128>>>(map_occ, feats, C, B, plane, canvas)));
+    TIME("v2 2 warps per CTA uniform", (k_fill<0, 64, kStage, 1, 2><<<blocks * 4, 64>>>(map_occ, feats, C, B, plane, canvas)));
+    TIME("v2 1 warp per CTA uniform", (k_fill<0, 64, kStage, 1, 1><<<blocks * 8, 32>>>(map_occ, feats, C, B, plane, canvas)));
+    TIME("v2 2 warps per CTA clustered", (k_fill<0, 64, kStage, 1, 2><<<blocks * 4, 64>>>(map_clu, feats, C, B, plane, canvas)));
+    TIME("v2 2 warps per CTA empty", (k_fill<0, 64, kStage, 1, 2><<<blocks * 4, 64>>>(map_empty, feats, C, B, plane, canvas)));
+    TIME("v2 16 warps per CTA uniform", (k_fill<0, 64, 576, 1, 16><<<blocks / 2, 512>>>(map_occ, feats, C, B, plane, canvas)));
     return 0;
 }
