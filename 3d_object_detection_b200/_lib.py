@@ -10,7 +10,7 @@ from pathlib import Path
 LIB_PATH = Path(__file__).resolve().parent / "lib" / "libpillarfront.so"
 
 EXPORTS = ["pf_version", "pf_last_error_string", "pf_create", "pf_destroy", "pf_workspace_bytes",
-           "pf_voxelize", "pf_voxelize_decorate", "pf_decorate", "pf_scatter", "pf_scatter_from_map",
+           "pf_voxelize", "pf_voxelize_decorate", "pf_voxelize_pfn", "pf_pfn", "pf_decorate", "pf_scatter", "pf_scatter_from_map",
            "pf_scatter_backward"]
 
 
@@ -54,6 +54,13 @@ def load():
     L.pf_voxelize_decorate.argtypes = [_p, _p, _p, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int,
                                        C.c_float, C.c_float, C.c_float, C.c_float, C.c_int,
                                        _p, _p, _p, _p, _p, _p]
+    L.pf_voxelize_pfn.restype = C.c_int
+    L.pf_voxelize_pfn.argtypes = [_p, _p, _p, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int,
+                                  C.c_float, C.c_float, C.c_float, C.c_float, C.c_int,
+                                  _p, _p, _p, C.c_int, _p, _p, _p, _p, _p, _p, _p]
+    L.pf_pfn.restype = C.c_int
+    L.pf_pfn.argtypes = [_p, _p, _p, C.c_int, C.c_int64, C.c_int, C.c_int,
+                         C.c_float, C.c_float, C.c_float, C.c_float, _p, _p, _p, C.c_int, _p, _p]
     L.pf_decorate.restype = C.c_int
     L.pf_decorate.argtypes = [_p, _p, _p, C.c_int, C.c_int64, C.c_int, C.c_int,
                               C.c_float, C.c_float, C.c_float, C.c_float, _p, _p]

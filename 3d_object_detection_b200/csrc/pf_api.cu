@@ -198,6 +198,42 @@ int pf_voxelize_decorate(pf_handle *h, const float *points, const int32_t *frame
     return voxelize_common(h, a, stream, "pf_voxelize_decorate");
 }
 
+int pf_voxelize_pfn(pf_handle *h, const float *points, const int32_t *frame_offsets, int n_frames, int max_frame_points,
+                    int point_stride, int compact, int coors_stride, float vx, float vy, float x_off, float y_off,
+                    int keep_cell_map, const float *pfn_weight, const float *pfn_scale, const float *pfn_shift, int n_ch,
+                    float *voxels, int32_t *coors, int32_t *num_points, int32_t *voxel_num, float *features,
+                    float *pillar_feats, void *stream)
+{
+    if (n_ch != 64) return fail(PF_ERR_UNSUPPORTED, "pf_voxelize_pfn: n_ch must be 64 (got %d)", n_ch);
+    if (!pfn_weight || !pfn_scale || !pfn_shift || !pillar_feats) return fail(PF_ERR_INVALID_ARGUMENT, "pf_voxelize_pfn: null PFN argument");
+    if (h && (h->p.F != 4 || point_stride != 4)) return fail(PF_ERR_UNSUPPORTED, "pf_voxelize_pfn: needs 4 floats per point (F = 4, stride 4)");
+    if (!aligned16(pillar_feats) || !aligned16(points)) return fail(PF_ERR_INVALID_ARGUMENT, "pf_voxelize_pfn: points / pillar_feats must be 16-byte aligned");
+    pf::VoxelizeArgs a{};
+    a.points = points, a.frame_offsets = frame_offsets, a.n_frames = n_frames, a.max_frame_points = max_frame_points;
+    a.point_stride = point_stride, a.compact = compact, a.coors_stride = coors_stride;
+    a.vx = vx, a.vy = vy, a.x_off = x_off, a.y_off = y_off, a.keep_cell_map = keep_cell_map;
+    a.voxels = voxels, a.coors = coors, a.num_points = num_points, a.voxel_num = voxel_num, a.features = features;
+    a.pfn_w = pfn_weight, a.pfn_scale = pfn_scale, a.pfn_shift = pfn_shift, a.pfn_out = pillar_feats;
+    return voxelize_common(h, a, stream, "pf_voxelize_pfn");
+}
+
+int pf_pfn(const float *voxels, const int32_t *num_points, const int32_t *coors, int coors_stride, int64_t n_voxels,
+           int max_points, int num_features, float vx, float vy, float x_off, float y_off, const float *pfn_weight,
+           const float *pfn_scale, const float *pfn_shift, int n_ch, float *pillar_feats, void *stream)
+{
+    if (n_voxels < 0) return fail(PF_ERR_INVALID_ARGUMENT, "pf_pfn: n_voxels < 0");
+    if (n_voxels == 0) return PF_OK;
+    if (!voxels || !num_points || !coors || !pfn_weight || !pfn_scale || !pfn_shift || !pillar_feats)
+        return fail(PF_ERR_INVALID_ARGUMENT, "pf_pfn: null argument");
+    if (n_ch != 64 || num_features != 4) return fail(PF_ERR_UNSUPPORTED, "pf_pfn: needs n_ch == 64 and num_features == 4");
+    if (coors_stride < 2 || max_points < 1 || max_points > 512) return fail(PF_ERR_UNSUPPORTED, "pf_pfn: coors_stride >= 2, 1 <= max_points <= 512");
+    if (!aligned16(voxels) || !aligned16(pillar_feats)) return fail(PF_ERR_INVALID_ARGUMENT, "pf_pfn: voxels / pillar_feats must be 16-byte aligned");
+    cudaError_t e = pf::launch_decorate(voxels, num_points, coors, coors_stride, n_voxels, max_points, num_features, vx, vy,
+                                        x_off, y_off, nullptr, static_cast<cudaStream_t>(stream), pfn_weight, pfn_scale,
+                                        pfn_shift, pillar_feats);
+    return e == cudaSuccess ? PF_OK : cuda_fail(e, "pf_pfn");
+}
+
 int pf_decorate(const float *voxels, const int32_t *num_points, const int32_t *coors, int coors_stride,
                 int64_t n_voxels, int max_points, int num_features, float vx, float vy, float x_off, float y_off,
                 float *features, void *stream)

@@ -22,7 +22,7 @@ constexpr int kG4Warps = 8;
 __host__ __device__ inline int g4_warp_floats(int vpw, int P) { return (vpw * P * 9 + 4 + 3) & ~3; }
 
 // PT > 0: compile-time max_points; PT == 0: runtime p.P
-template <int GROUP, int PT, bool FROM_POINTS>
+template <int GROUP, int PT, bool FROM_POINTS, bool PFN>
 __global__ void __launch_bounds__(kG4Warps * 32) k_gather4(Params p, Work w, GatherArgs a)
 {
     constexpr int VPW = 32 / GROUP;   // voxels per warp
@@ -74,7 +74,7 @@ __global__ void __launch_bounds__(kG4Warps * 32) k_gather4(Params p, Work w, Gat
     const float4 *src4 = FROM_POINTS ? reinterpret_cast<const float4 *>(a.points) + pt_base
                                      : reinterpret_cast<const float4 *>(a.voxels_in) + (size_t)v * P;
     const int32_t *slots = FROM_POINTS ? w.slotidx + ((size_t)f * p.max_voxels + v) * P : nullptr;
-    const bool want_f = a.features != nullptr;
+    const bool want_f = PFN || a.features != nullptr;   // stage the decorated rows
 
     // pass 1: fetch the rows, store the voxel rows, stage x,y,z,i, accumulate the xyz sums
     float sx = 0.f, sy = 0.f, sz = 0.f;
@@ -173,6 +173,38 @@ __global__ void __launch_bounds__(kG4Warps * 32) k_gather4(Params p, Work w, Gat
     }
     __syncwarp();
 
+    if (PFN) {
+        // Fused pillar feature net (networks/pointpillars8_shared.py:24-28,57-60 in eval mode): Conv1d(9 -> 64, k = 1,
+        // no bias) + folded BatchNorm1d + ReLU + max over the P slots.  A lane owns two channels and keeps their 18
+        // weights in registers; the staged feature rows are read as shared-memory broadcasts.  Padded slots are zero
+        // rows, i.e. the candidate relu(shift): taken once when the pillar is not full instead of P - cnt times.
+        const int c0 = lane * 2;
+        float w0[9], w1[9];
+#pragma unroll
+        for (int k = 0; k < 9; ++k) w0[k] = __ldg(a.pfn_w + c0 * 9 + k), w1[k] = __ldg(a.pfn_w + (c0 + 1) * 9 + k);
+        const float sc0 = __ldg(a.pfn_scale + c0), sc1 = __ldg(a.pfn_scale + c0 + 1);
+        const float sh0 = __ldg(a.pfn_shift + c0), sh1 = __ldg(a.pfn_shift + c0 + 1);
+        for (int q = 0; q < nvw; ++q) {
+            const int cnt_q = __shfl_sync(0xffffffffu, cnt, q * GROUP);
+            const float *fr = s_w + phase + q * (P * 9);
+            float m0 = cnt_q < P ? sh0 : -3.402823466e38f, m1 = cnt_q < P ? sh1 : -3.402823466e38f;
+#pragma unroll 2
+            for (int r = 0; r < cnt_q; ++r) {
+                float d0 = 0.f, d1 = 0.f;
+#pragma unroll
+                for (int k = 0; k < 9; ++k) {
+                    const float fv = fr[r * 9 + k];
+                    d0 = fmaf(fv, w0[k], d0);
+                    d1 = fmaf(fv, w1[k], d1);
+                }
+                m0 = fmaxf(m0, fmaf(d0, sc0, sh0));
+                m1 = fmaxf(m1, fmaf(d1, sc1, sh1));
+            }
+            *reinterpret_cast<float2 *>(a.pfn_out + (row0 + q) * 64 + c0) = make_float2(fmaxf(m0, 0.f), fmaxf(m1, 0.f));
+        }
+        if (!a.features) return;
+    }
+
     // copy-out: the warp's nvw*P*9 floats are contiguous in the output
     const int total = nvw * (P * 9);
     float *gdst = a.features + row0 * (P * 9);
@@ -188,21 +220,29 @@ __global__ void __launch_bounds__(kG4Warps * 32) k_gather4(Params p, Work w, Gat
     if (lane < total - done) gdst[done + lane] = ssrc[done + lane];
 }
 
-template <int GROUP, int PT, bool FROM_POINTS>
-static cudaError_t run_g4(const Params &p, const Work &w, const GatherArgs &a, long long voxels, int n_frames,
-                          cudaStream_t stream)
+template <int GROUP, int PT, bool FROM_POINTS, bool PFN>
+static cudaError_t run_g4x(const Params &p, const Work &w, const GatherArgs &a, long long voxels, int n_frames,
+                           cudaStream_t stream)
 {
     constexpr int VPW = 32 / GROUP;
     const size_t smem = (size_t)kG4Warps * g4_warp_floats(VPW, p.P) * sizeof(float);
     if (smem > 48 * 1024) {
-        cudaError_t e = cudaFuncSetAttribute(k_gather4<GROUP, PT, FROM_POINTS>,
+        cudaError_t e = cudaFuncSetAttribute(k_gather4<GROUP, PT, FROM_POINTS, PFN>,
                                              cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
         if (e != cudaSuccess) return e;
     }
     const long long per_cta = (long long)kG4Warps * VPW;
     const dim3 grid((unsigned)((voxels + per_cta - 1) / per_cta), (unsigned)n_frames);
-    k_gather4<GROUP, PT, FROM_POINTS><<<grid, kG4Warps * 32, smem, stream>>>(p, w, a);
+    k_gather4<GROUP, PT, FROM_POINTS, PFN><<<grid, kG4Warps * 32, smem, stream>>>(p, w, a);
     return cudaGetLastError();
+}
+
+template <int GROUP, int PT, bool FROM_POINTS>
+static cudaError_t run_g4(const Params &p, const Work &w, const GatherArgs &a, long long voxels, int n_frames,
+                          cudaStream_t stream)
+{
+    return a.pfn_w ? run_g4x<GROUP, PT, FROM_POINTS, true>(p, w, a, voxels, n_frames, stream)
+                   : run_g4x<GROUP, PT, FROM_POINTS, false>(p, w, a, voxels, n_frames, stream);
 }
 
 template <bool FROM_POINTS>
@@ -230,6 +270,7 @@ cudaError_t launch_gather4(const Params &p, const Work &w, const GatherArgs &a, 
         if (!al16(a.voxels_in) || a.n_voxels >= (1ll << 31)) return cudaErrorNotSupported;
     }
     if (a.features && !al16(a.features)) return cudaErrorNotSupported;
+    if (a.pfn_w && (!a.pfn_scale || !a.pfn_shift || !a.pfn_out || (reinterpret_cast<uintptr_t>(a.pfn_out) & 7))) return cudaErrorNotSupported;
     if (from_points) return pick_g4<true>(p, w, a, p.max_voxels, n_frames, stream);
     return pick_g4<false>(p, w, a, a.n_voxels, 1, stream);
 }

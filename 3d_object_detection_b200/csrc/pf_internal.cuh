@@ -60,6 +60,8 @@ struct VoxelizeArgs {
     int32_t *num_points;
     int32_t *voxel_num;
     float *features;
+    const float *pfn_w, *pfn_scale, *pfn_shift;   // optional fused PFN (pf_voxelize_pfn)
+    float *pfn_out;
 };
 
 // arguments of the per-voxel gather + decoration kernels (pf_voxelize.cu generic, pf_gather.cu F = 4)
@@ -78,6 +80,11 @@ struct GatherArgs {
     int32_t *coors;                  // may be null
     int32_t *num_points;             // may be null
     float *features;                 // may be null
+    // fused pillar feature net (eval mode): out[v][c] = max_p relu(scale[c] * <w[c], feature row p> + shift[c]), 64 channels
+    const float *pfn_w;              // [64][F+5] = Conv1d weight (64, 9, 1); null = no PFN
+    const float *pfn_scale;          // [64] gamma / sqrt(running_var + eps)
+    const float *pfn_shift;          // [64] beta - running_mean * scale
+    float *pfn_out;                  // [rows][64]
 };
 
 // launchers (pf_voxelize.cu / pf_scatter.cu); all asynchronous on `stream`, return the launch error.
@@ -88,7 +95,8 @@ cudaError_t launch_gather4(const Params &p, const Work &w, const GatherArgs &a, 
 cudaError_t launch_voxelize(const Params &p, const Work &w, const VoxelizeArgs &a, cudaStream_t stream);
 cudaError_t launch_decorate(const float *voxels, const int32_t *num, const int32_t *coors, int coors_stride,
                             int64_t n_voxels, int P, int F, float vx, float vy, float x_off, float y_off,
-                            float *features, cudaStream_t stream);
+                            float *features, cudaStream_t stream, const float *pfn_w = nullptr,
+                            const float *pfn_scale = nullptr, const float *pfn_shift = nullptr, float *pfn_out = nullptr);
 cudaError_t launch_scatter(const Params &p, const Work &w, const float *feats, int64_t sv, int64_t sc,
                            const int32_t *coors, int coors_stride, int64_t n_voxels, int batch, int n_ch,
                            float *canvas, cudaStream_t stream);

@@ -574,7 +574,9 @@ cudaError_t launch_voxelize(const Params &p, const Work &w, const VoxelizeArgs &
     ga.compact = a.compact, ga.coors_stride = a.coors_stride;
     ga.vx = a.vx, ga.vy = a.vy, ga.x_off = a.x_off, ga.y_off = a.y_off;
     ga.voxels = a.voxels, ga.coors = a.coors, ga.num_points = a.num_points, ga.features = a.features;
+    ga.pfn_w = a.pfn_w, ga.pfn_scale = a.pfn_scale, ga.pfn_shift = a.pfn_shift, ga.pfn_out = a.pfn_out;
     cudaError_t e = vec4 ? launch_gather4(p, w, ga, B, true, stream) : cudaErrorNotSupported;
+    if (e == cudaErrorNotSupported && a.pfn_w) return e;   // the fused PFN exists only on the F = 4 fast path
     if (e == cudaErrorNotSupported)   // generic F / stride / alignment
         e = dispatch_gather<true>(p, w, ga, dim3((p.max_voxels + 15) / 16, B), dim3((p.max_voxels + 7) / 8, B), vec4,
                                   stream);
@@ -584,7 +586,8 @@ cudaError_t launch_voxelize(const Params &p, const Work &w, const VoxelizeArgs &
 
 cudaError_t launch_decorate(const float *voxels, const int32_t *num, const int32_t *coors, int coors_stride,
                             int64_t n_voxels, int P, int F, float vx, float vy, float x_off, float y_off,
-                            float *features, cudaStream_t stream)
+                            float *features, cudaStream_t stream, const float *pfn_w, const float *pfn_scale,
+                            const float *pfn_shift, float *pfn_out)
 {
     if (n_voxels <= 0) return cudaSuccess;
     Params p{};
@@ -595,8 +598,9 @@ cudaError_t launch_decorate(const float *voxels, const int32_t *num, const int32
     ga.n_voxels = n_voxels;
     ga.vx = vx, ga.vy = vy, ga.x_off = x_off, ga.y_off = y_off;
     ga.features = features;
+    ga.pfn_w = pfn_w, ga.pfn_scale = pfn_scale, ga.pfn_shift = pfn_shift, ga.pfn_out = pfn_out;
     const cudaError_t e4 = launch_gather4(p, w, ga, 1, false, stream);
-    if (e4 != cudaErrorNotSupported) return e4;
+    if (e4 != cudaErrorNotSupported || pfn_w) return e4;   // the fused PFN exists only on the F = 4 fast path
     const unsigned b16 = (unsigned)((n_voxels + 15) / 16), b32 = (unsigned)((n_voxels + 7) / 8);
     return dispatch_gather<false>(p, w, ga, dim3(b16, 1), dim3(b32, 1), false, stream);
 }

@@ -61,6 +61,7 @@ class PillarFrontEnd:
         self.voxel_num = torch.zeros((self.B,), dtype=torch.int32, device=dev)
         self.features = torch.empty((rows, self.P, self.F + 5), dtype=torch.float32, device=dev)
         self.canvas = torch.empty((self.B, self.C, self.nx, self.ny), dtype=torch.float32, device=dev)
+        self.pillar_feats = None   # (rows, 64), allocated by the first voxelize_pfn
         self._graph = None
         self._g_inputs = None
 
@@ -79,6 +80,26 @@ class PillarFrontEnd:
             self.num_points.data_ptr(), self.voxel_num.data_ptr(), self.features.data_ptr(), stream),
             "pf_voxelize_decorate")
 
+    def voxelize_pfn(self, points, frame_offsets, folded, n_frames=None, max_frame_points=None, want_features=False):
+        """Fused voxelise + decorate + PFN (pf_voxelize_pfn): fills voxels/coors/num/voxel_num and ``self.pillar_feats``
+        (rows, 64); ``folded`` = (weight (64,9), scale, shift) from pillar_ops.fold_pfn / PointNet.folded()."""
+        n_frames = self.B if n_frames is None else int(n_frames)
+        mfp = self.max_points_per_frame if max_frame_points is None else int(max_frame_points)
+        if self.pillar_feats is None:
+            self.pillar_feats = torch.empty((self.B * self.max_voxels, 64), dtype=torch.float32, device=self.device)
+        w, sc, sh = folded
+        h = self.handle
+        vx, vy, xo, yo = self.consts
+        stream = torch.cuda.current_stream(self.device).cuda_stream
+        _lib.check(h.lib.pf_voxelize_pfn(
+            h.ptr, points.data_ptr(), frame_offsets.data_ptr(), n_frames, mfp, int(points.shape[1]),
+            1 if self.compact else 0, 4, vx, vy, xo, yo, 1, w.data_ptr(), sc.data_ptr(), sh.data_ptr(), 64,
+            self.voxels.data_ptr() if self.voxels is not None else None, self.coors.data_ptr(),
+            self.num_points.data_ptr(), self.voxel_num.data_ptr(),
+            self.features.data_ptr() if want_features else None, self.pillar_feats.data_ptr(), stream),
+            "pf_voxelize_pfn")
+        return self.pillar_feats
+
     def scatter(self, pillar_feats, n_frames=None):
         """pillar_feats: CUDA fp32 (rows, C) row-major, rows laid out like the voxel outputs."""
         n_frames = self.B if n_frames is None else int(n_frames)
@@ -91,9 +112,13 @@ class PillarFrontEnd:
 
     def step(self, points, frame_offsets, pillar_feats=None, pfn=None, n_frames=None, max_frame_points=None):
         """One pass of the hot path over one batch.  Exactly one of pillar_feats / pfn feeds the scatter."""
+        fused = pfn is not None and hasattr(pfn, "folded") and not getattr(pfn, "training", True) and self.F == 4
+        if fused:   # PointNet in eval mode: decorate + conv + BN + ReLU + max inside the gather kernel
+            return self.scatter(self.voxelize_pfn(points, frame_offsets, pfn.folded(), n_frames, max_frame_points),
+                                n_frames)
         self.voxelize_decorate(points, frame_offsets, n_frames, max_frame_points)
-        if pfn is not None:
-            pillar_feats = pfn(self.features)
+        if pfn is not None:   # PointNet in training mode -> its torch tail; any other callable maps features -> (rows, C)
+            pillar_feats = pfn.features_to_pillars(self.features) if hasattr(pfn, "features_to_pillars") else pfn(self.features)
         if pillar_feats is None:
             raise ValueError("step needs pillar_feats or pfn")
         return self.scatter(pillar_feats, n_frames)

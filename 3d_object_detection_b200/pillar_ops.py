@@ -66,8 +66,46 @@ def decorate(voxels, num_points, coors, vx, vy, x_offset, y_offset):
     return out
 
 
+def fold_pfn(pfn_layers):
+    """Fold ``pfn_layers`` = Conv1d(9->64, k=1, bias=False) + BatchNorm1d (eval) + ReLU of the reference
+    (pointpillars8_shared.py:24-28) into (weight (64, 9), scale (64,), shift (64,)) fp32 contiguous tensors:
+    ``relu(bn(conv(x))) == relu(scale * (weight @ x) + shift)`` with scale = gamma / sqrt(var + eps),
+    shift = beta - mean * scale."""
+    conv, bn = pfn_layers[0], pfn_layers[1]
+    if conv.bias is not None or conv.kernel_size != (1,) or conv.out_channels != 64:
+        raise ValueError("fold_pfn expects Conv1d(C_in, 64, kernel_size=1, bias=False)")
+    with torch.no_grad():
+        w = conv.weight.detach().reshape(conv.out_channels, conv.in_channels).to(torch.float32).contiguous()
+        gamma = bn.weight.detach().float() if bn.affine else torch.ones_like(bn.running_var)
+        beta = bn.bias.detach().float() if bn.affine else torch.zeros_like(bn.running_var)
+        scale = (gamma / torch.sqrt(bn.running_var.detach().float() + bn.eps)).contiguous()
+        shift = (beta - bn.running_mean.detach().float() * scale).contiguous()
+    return w, scale, shift
+
+
+def pfn_fused(voxels, num_points, coors, vx, vy, x_offset, y_offset, weight, scale, shift):
+    """decorate + Conv1d/BN(eval)/ReLU + max over the points in ONE kernel (pf_pfn): (V,P,4) -> (V,64)."""
+    _require_cuda(voxels, "voxels")
+    if voxels.dtype != torch.float32 or voxels.dim() != 3 or voxels.shape[2] != 4:
+        raise ValueError(f"pfn_fused needs float32 (V, P, 4) voxels, got {voxels.dtype} {tuple(voxels.shape)}")
+    v, p, f = voxels.shape
+    voxels = voxels.contiguous()
+    num_points = num_points.to(device=voxels.device, dtype=torch.int32).contiguous()
+    coors = coors.to(device=voxels.device, dtype=torch.int32).contiguous()
+    out = torch.empty((v, 64), dtype=torch.float32, device=voxels.device)
+    lib = _lib.load()
+    with torch.cuda.device(voxels.device):
+        stream = torch.cuda.current_stream(voxels.device).cuda_stream
+        _lib.check(lib.pf_pfn(voxels.data_ptr(), num_points.data_ptr(), coors.data_ptr(), int(coors.shape[1]), v, p, f,
+                              vx, vy, x_offset, y_offset, weight.data_ptr(), scale.data_ptr(), shift.data_ptr(), 64,
+                              out.data_ptr(), stream), "pf_pfn")
+    return out
+
+
 class PointNet(nn.Module):
-    """Pillar feature net front: CUDA decoration + the reference's learned ``pfn_layers`` (torch/cuDNN)."""
+    """Pillar feature net: CUDA decoration + the reference's learned ``pfn_layers``.  In eval mode with 4-float
+    points the whole forward (decorate, conv, folded BN, ReLU, max) is one fused CUDA kernel (pf_pfn); in training
+    mode (batch statistics, autograd through the conv) the PFN runs in torch on the CUDA-decorated features."""
 
     def __init__(self, num_input_features, voxel_size, offset):
         super().__init__()
@@ -82,7 +120,27 @@ class PointNet(nn.Module):
     def decorate(self, voxels, num_point_per_voxel, coors):
         return decorate(voxels, num_point_per_voxel, coors, self.vx, self.vy, self.x_offset, self.y_offset)
 
+    def features_to_pillars(self, features):
+        """The learned tail of forward() on already decorated (V, P, 9) features, in torch (any mode)."""
+        x = self.pfn_layers(features.permute(0, 2, 1).contiguous()).permute(0, 2, 1).contiguous()
+        return torch.max(x, dim=1, keepdim=True)[0].squeeze(1)
+
+    def folded(self):
+        """(weight, scale, shift) of fold_pfn, cached until a parameter or running statistic changes."""
+        conv, bn = self.pfn_layers[0], self.pfn_layers[1]
+        ts = [conv.weight, bn.weight, bn.bias, bn.running_mean, bn.running_var]
+        key = tuple((t.data_ptr(), t._version) for t in ts if t is not None)
+        if getattr(self, "_fold_key", None) != key:
+            self._fold = fold_pfn(self.pfn_layers)
+            self._fold_key = key
+        return self._fold
+
     def forward(self, voxels, num_point_per_voxel, coors):
+        if (not self.training and voxels.is_cuda and voxels.dtype == torch.float32 and voxels.dim() == 3
+                and voxels.shape[2] == 4 and self.pfn_layers[0].weight.is_cuda):
+            w, sc, sh = self.folded()
+            return pfn_fused(voxels, num_point_per_voxel, coors, self.vx, self.vy, self.x_offset, self.y_offset,
+                             w, sc, sh).squeeze()
         features = self.decorate(voxels, num_point_per_voxel, coors)
         x = self.pfn_layers(features.permute(0, 2, 1).contiguous()).permute(0, 2, 1).contiguous()
         return torch.max(x, dim=1, keepdim=True)[0].squeeze()

@@ -14,6 +14,8 @@
  *                            networks/pointpillars8_export.py:44-51      (Scatter.run, channel-major features),
  *                            networks/pointpillars8_trt.py:139-205       (Scatter_cuda + its CUDA-C kernel)
  *   pf_scatter_backward  <-> autograd of the index_put in pointpillars8_shared.py:100 (a gather)
+ *   pf_pfn / pf_voxelize_pfn <-> networks/pointpillars8_shared.py:24-28, 57-60 (pfn_layers + max, eval mode), fused
+ *                            behind the decoration ("next" row N1)
  *
  * Conventions
  *   - plain pointers and sizes only; every pointer named *device* is CUDA device memory on the handle's
@@ -100,6 +102,28 @@ PF_API int pf_voxelize_decorate(pf_handle *h, const float *points, const int32_t
                          float vx, float vy, float x_off, float y_off, int keep_cell_map,
                          float *voxels, int32_t *coors, int32_t *num_points, int32_t *voxel_num,
                          float *features, void *stream);
+
+/* "Next" row N1: voxelise + decorate + the pillar feature net in one pass, eval mode --
+ *   pillar_feats[row][c] = max_p relu(scale[c] * <weight[c][0..9), feature row p> + shift[c]),  c < 64
+ * i.e. Conv1d(9 -> 64, k = 1, bias = False) + BatchNorm1d (running statistics folded into scale / shift by the
+ * caller: scale = gamma / sqrt(var + eps), shift = beta - mean * scale) + ReLU + max over the P slots, exactly the
+ * tail of PointNet.forward (networks/pointpillars8_shared.py:24-28, 57-60).  The (rows, P, 9) feature tensor never
+ * touches HBM unless `features` is non-NULL.  Needs F == 4, point_stride == 4, n_ch == 64.
+ *   pfn_weight  device float [64][9]   (Conv1d weight (64, 9, 1), contiguous)
+ *   pillar_feats device float [rows][64]   row layout as the other outputs (slab / compact) */
+PF_API int pf_voxelize_pfn(pf_handle *h, const float *points, const int32_t *frame_offsets, int n_frames,
+                    int max_frame_points, int point_stride, int compact, int coors_stride,
+                    float vx, float vy, float x_off, float y_off, int keep_cell_map,
+                    const float *pfn_weight, const float *pfn_scale, const float *pfn_shift, int n_ch,
+                    float *voxels, int32_t *coors, int32_t *num_points, int32_t *voxel_num,
+                    float *features, float *pillar_feats, void *stream);
+
+/* Stand-alone decorate + PFN of already voxelised pillars: PointNet.forward in eval mode
+ * (networks/pointpillars8_shared.py:30-60) -> pillar_feats float [n_voxels][64]. */
+PF_API int pf_pfn(const float *voxels, const int32_t *num_points, const int32_t *coors, int coors_stride,
+           int64_t n_voxels, int max_points, int num_features, float vx, float vy, float x_off, float y_off,
+           const float *pfn_weight, const float *pfn_scale, const float *pfn_shift, int n_ch,
+           float *pillar_feats, void *stream);
 
 /* Stand-alone decoration of already voxelised pillars (host-known row count). */
 PF_API int pf_decorate(const float *voxels, const int32_t *num_points, const int32_t *coors, int coors_stride,

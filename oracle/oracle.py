@@ -192,3 +192,14 @@ class FrontendBatch:
         if tot < 0:
             raise MemoryError("oracle_frontend_batch: allocation failed")
         return int(tot)
+
+
+def pfn(features, weight, gamma, beta, mean, var, eps=1e-5):
+    """fp64 restatement of the learned tail of PointNet.forward in eval mode (pointpillars8_shared.py:24-28,57-60):
+    Conv1d(9->64, k=1, no bias) + BatchNorm1d(running stats) + ReLU + max over the P slots -> (V, 64)."""
+    f = np.asarray(features, np.float64)                      # (V, P, 9)
+    w = np.asarray(weight, np.float64).reshape(-1, f.shape[2])  # (64, 9)
+    y = f @ w.T                                               # (V, P, 64)
+    y = (y - np.asarray(mean, np.float64)) / np.sqrt(np.asarray(var, np.float64) + eps) * np.asarray(gamma, np.float64) \
+        + np.asarray(beta, np.float64)
+    return np.maximum(y, 0.0).max(axis=1)

@@ -150,3 +150,69 @@ def test_pipeline_full_size_checksums(pf):
     c1 = canvas.clone()
     assert torch.equal(fe.step(pts, offs, pillar_feats=pillar), c1)
     fe.close()
+
+
+# ------------------------------------------------------------------------------------------------ fused PFN (N1)
+def _random_pointnet(pf, cfg, geom, seed):
+    torch.manual_seed(seed)
+    net = pf.PointNet(cfg["num_point_features"], cfg["voxel_size"], geom.offset).cuda()
+    bn = net.pfn_layers[1]
+    with torch.no_grad():   # non-trivial running statistics and affine terms, some shifts positive (padding can win the max)
+        bn.running_mean.copy_(torch.randn(64) * 0.5)
+        bn.running_var.copy_(torch.rand(64) * 2 + 0.1)
+        bn.weight.copy_(torch.randn(64))
+        bn.bias.copy_(torch.randn(64) * 0.5)
+        net.pfn_layers[0].weight.mul_(3.0)
+    return net.eval()
+
+
+@pytest.mark.parametrize("gkey", util.GRID_KEYS)
+@pytest.mark.parametrize("name", ["s1", "s2_ring", "dense_cap", "n5"])
+def test_fused_pfn_matches_reference_math(pf, gkey, name):
+    """pf_pfn (decorate + conv + folded BN + ReLU + max in one kernel) against an fp64 restatement evaluated on the
+    REFERENCE's own decorated features, and against the unfused torch modules."""
+    g = util.load_small(gkey, name)
+    cfg = util.small_config(gkey, g)
+    geom = cfgmod.derive_grid(cfg)
+    net = _random_pointnet(pf, cfg, geom, 3)
+    conv, bn = net.pfn_layers[0], net.pfn_layers[1]
+    v, n, c = (torch.from_numpy(g[k]).cuda() for k in ("voxels", "num", "coors"))
+    with torch.no_grad():
+        got = net(v, n, c).reshape(len(g["num"]), 64).cpu().numpy()
+        unfused = net.features_to_pillars(net.decorate(v, n, c)).cpu().numpy()
+    finite = np.isfinite(g["features"]).all(axis=(1, 2))           # s4-style NaN payloads are not in these fixtures
+    want = oracle.pfn(g["features"], conv.weight.detach().cpu().numpy(), bn.weight.detach().cpu().numpy(),
+                      bn.bias.detach().cpu().numpy(), bn.running_mean.cpu().numpy(), bn.running_var.cpu().numpy(), bn.eps)
+    scale = np.abs(g["features"]).reshape(len(finite), -1).max(axis=1, keepdims=True) + 1.0
+    # fp32 conv of 9 terms of magnitude <= scale, times a BN gain of up to ~10: 1e-4 relative to the operand magnitude
+    assert np.all(np.abs(got[finite] - want[finite]) <= 1e-4 * scale[finite] + 1e-4 * np.abs(want[finite])), \
+        np.abs(got - want).max()
+    assert np.allclose(got, unfused, rtol=1e-4, atol=1e-4 * float(scale.max()))
+    assert (got >= 0).all()
+
+
+@pytest.mark.parametrize("gkey", ["20cm", "nuscene"])
+def test_pipeline_with_fused_pfn(pf, gkey):
+    """PillarFrontEnd.step(pfn=PointNet.eval()) = pf_voxelize_pfn + fill, against voxelise -> torch PFN -> scatter."""
+    cfg = cfgmod.builtin_config(gkey)
+    cfg["max_voxels"] = 700
+    geom = cfgmod.derive_grid(cfg)
+    frames = [synth.make_frame(k, geom, n, 40 + i, 500) for i, (k, n) in enumerate([("S1", 9000), ("S3", 3000), ("S2", 8192)])]
+    net = _random_pointnet(pf, cfg, geom, 5)
+    fe = pf.PillarFrontEnd(cfg, max_batch=3, max_points_per_frame=9000, device=0)
+    pts = torch.from_numpy(np.concatenate(frames)).cuda()
+    offs = torch.tensor(np.concatenate([[0], np.cumsum([len(f) for f in frames])]).astype(np.int32)).cuda()
+    with torch.no_grad():
+        canvas = fe.step(pts, offs, pfn=net).clone()
+        fused_rows = fe.pillar_feats.clone()
+        fe.voxelize_decorate(pts, offs)
+        want_rows = net.features_to_pillars(fe.features)
+    counts = fe.voxel_num.cpu().numpy()
+    for f in range(3):
+        lo = f * cfg["max_voxels"]
+        a, b = fused_rows[lo:lo + counts[f]], want_rows[lo:lo + counts[f]]
+        assert torch.allclose(a, b, rtol=1e-4, atol=2e-3), (a - b).abs().max()
+        coors = fe.coors[lo:lo + counts[f]].cpu().numpy()
+        want_canvas = oracle.scatter(a.cpu().numpy(), coors[:, :3], fe.nx, fe.ny)[0]
+        assert np.array_equal(canvas[f].cpu().numpy(), want_canvas)      # the fill itself stays bit-exact
+    fe.close()
