@@ -43,6 +43,7 @@ def parse_args():
     ap.add_argument("--batch", type=int, default=0, help="frames per GPU per step (default: 8; 10cm: 32)")
     ap.add_argument("--cpu-seconds", type=float, default=12.0, help="CPU-baseline sample budget")
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-pfn", action="store_true", help="skip the fused-vs-torch PFN side measurement")
     ap.add_argument("--device-pipelines", type=int, default=1,
                     help="device-resident arm: front ends (workspace + graph) in flight; 1 = strictly serial steps (default: the "
                          "fill kernel fills the GPU, so a second batch in flight gains only ~5 %% at 20 cm and loses at 10 cm)")
@@ -284,6 +285,35 @@ def run_b200(args, rank, world, local):
     t_vox = float(np.mean([st[3 * i].elapsed_time(st[3 * i + 1]) for i in range(K)])) * 1e-3
     t_scat = float(np.mean([st[3 * i + 1].elapsed_time(st[3 * i + 2]) for i in range(K)])) * 1e-3
 
+    # ---------------- next-row N1: the learned PFN in the loop, fused vs torch (reported beside, not the headline) ----
+    with_pfn = None
+    if not args.no_pfn:
+        net = pfm.PointNet(4, cfg["voxel_size"], geom.offset).to(dev).eval()
+
+        def unfused():
+            fe.voxelize_decorate(pts_d, offs_d)
+            fe.scatter(net.features_to_pillars(fe.features))
+
+        def t_of(fn, n):
+            with torch.no_grad():
+                for _ in range(3):
+                    fn()
+                torch.cuda.synchronize(dev)
+                a0, a1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+                a0.record()
+                for _ in range(n):
+                    fn()
+                a1.record()
+                torch.cuda.synchronize(dev)
+            return a0.elapsed_time(a1) / n
+
+        n_pfn = max(5, min(K, 40))
+        with_pfn = {"fused_ms_per_step": t_of(lambda: fe.step(pts_d, offs_d, pfn=net), n_pfn),
+                    "torch_pfn_ms_per_step": t_of(unfused, max(3, n_pfn // 4)),
+                    "note": "eager; random-init PointNet.eval(); fused = pf_voxelize_pfn (decorate + Conv1d 9->64 + folded BN "
+                            "+ ReLU + max in the gather kernel) + fill; torch = CUDA decoration -> pfn_layers in torch -> fill"}
+        del net
+
     # ---------------- end-to-end arm: public API, pinned host points in, coords/counts out ----------------
     depth = max(1, args.pipelines)
     pipes = []
@@ -334,7 +364,7 @@ def run_b200(args, rank, world, local):
         dist.barrier()
         dist.destroy_process_group()
     return dict(cfg=cfg, geom=geom, frames=frames, B=B, K=K, W=W, t_dev=t_dev, t_e2e=t_e2e, t_vox=t_vox,
-                t_scat=t_scat, w_e2e=w_e2e, t_serial=t_serial, d_dev=d_dev, counts=counts, bytes_alg=bytes_alg, n_points=n_points, tot_pts=tot_pts,
+                t_scat=t_scat, with_pfn=with_pfn, w_e2e=w_e2e, t_serial=t_serial, d_dev=d_dev, counts=counts, bytes_alg=bytes_alg, n_points=n_points, tot_pts=tot_pts,
                 tot_frames=tot_frames, clocks=clocks, h2d=h2d, d2h=d2h, fe=fe, depth=depth, world=world)
 
 
@@ -398,6 +428,7 @@ def main():
         "clocks": r["clocks"],
         "stages_ms": {"voxelize_decorate": 1e3 * r["t_vox"], "scatter": 1e3 * r["t_scat"]},
         "bytes_per_step": r["bytes_alg"],
+        "with_pfn": r["with_pfn"],
         "e2e_hbm_frac": r["bytes_alg"]["e2e"] / (r["t_dev"] / K) / 1e9 / peak,
         "e2e_hbm_frac_serial": r["bytes_alg"]["e2e"] / (r["t_serial"] / K) / 1e9 / peak,
         "roofline": {"kernel": "k_canvas_fill (pf_scatter_from_map)", "bound": "hbm", "achieved": achieved,
