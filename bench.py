@@ -43,6 +43,7 @@ def parse_args():
     ap.add_argument("--batch", type=int, default=0, help="frames per GPU per step (default: 8; 10cm: 32)")
     ap.add_argument("--cpu-seconds", type=float, default=12.0, help="CPU-baseline sample budget")
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-single", action="store_true", help="skip the single-frame drop-in latency measurement")
     ap.add_argument("--no-pfn", action="store_true", help="skip the fused-vs-torch PFN side measurement")
     ap.add_argument("--device-pipelines", type=int, default=1,
                     help="device-resident arm: front ends (workspace + graph) in flight; 1 = strictly serial steps (default: the "
@@ -314,6 +315,37 @@ def run_b200(args, rank, world, local):
                             "+ ReLU + max in the gather kernel) + fill; torch = CUDA decoration -> pfn_layers in torch -> fill"}
         del net
 
+    # ---------------- drop-in single-frame latency: the reference's own call sequence (InferData.get + forward) -------
+    single = None
+    if rank == 0 and not args.no_single:
+        vg = pfm.VoxelGenerator(dict(cfg), device=local, max_points_per_frame=n_pts_frame)
+        net1 = pfm.PointNet(4, cfg["voxel_size"], geom.offset).to(dev).eval()
+        scat1 = pfm.PointPillarsScatter(1, geom.grid_size, 64)
+        frame0 = frames[0]
+
+        def one_frame(device_outputs):
+            v, c, n = vg.generate(frame0, device_outputs=device_outputs)       # numpy in (pageable), like dataset.py:215
+            if not device_outputs:                                             # example_convert_to_torch, utils.py:7-20
+                v, c, n = (torch.as_tensor(x, device=dev) for x in (v, c, n))
+            with torch.no_grad():
+                canvas1 = scat1(net1(v, n, c).reshape(-1, 64), c)
+            torch.cuda.synchronize(dev)
+            return canvas1
+
+        lat = {}
+        for key, dev_out in (("numpy_outputs", False), ("device_outputs", True)):
+            for _ in range(5):
+                one_frame(dev_out)
+            t0 = time.perf_counter()
+            reps = 30
+            for _ in range(reps):
+                one_frame(dev_out)
+            lat[key + "_ms_per_frame"] = 1e3 * (time.perf_counter() - t0) / reps
+        single = dict(lat, frame_points=int(len(frame0)),
+                      api="VoxelGenerator.generate(numpy points) -> PointNet.eval() (fused PFN) -> PointPillarsScatter, "
+                          "batch 1, host wall clock incl. H2D, the voxel-count read-back and a final synchronize")
+        vg.close()
+
     # ---------------- end-to-end arm: public API, pinned host points in, coords/counts out ----------------
     depth = max(1, args.pipelines)
     pipes = []
@@ -364,7 +396,7 @@ def run_b200(args, rank, world, local):
         dist.barrier()
         dist.destroy_process_group()
     return dict(cfg=cfg, geom=geom, frames=frames, B=B, K=K, W=W, t_dev=t_dev, t_e2e=t_e2e, t_vox=t_vox,
-                t_scat=t_scat, with_pfn=with_pfn, w_e2e=w_e2e, t_serial=t_serial, d_dev=d_dev, counts=counts, bytes_alg=bytes_alg, n_points=n_points, tot_pts=tot_pts,
+                t_scat=t_scat, with_pfn=with_pfn, single=single, w_e2e=w_e2e, t_serial=t_serial, d_dev=d_dev, counts=counts, bytes_alg=bytes_alg, n_points=n_points, tot_pts=tot_pts,
                 tot_frames=tot_frames, clocks=clocks, h2d=h2d, d2h=d2h, fe=fe, depth=depth, world=world)
 
 
@@ -429,6 +461,7 @@ def main():
         "stages_ms": {"voxelize_decorate": 1e3 * r["t_vox"], "scatter": 1e3 * r["t_scat"]},
         "bytes_per_step": r["bytes_alg"],
         "with_pfn": r["with_pfn"],
+        "single_frame_api": r["single"],
         "e2e_hbm_frac": r["bytes_alg"]["e2e"] / (r["t_dev"] / K) / 1e9 / peak,
         "e2e_hbm_frac_serial": r["bytes_alg"]["e2e"] / (r["t_serial"] / K) / 1e9 / peak,
         "roofline": {"kernel": "k_canvas_fill (pf_scatter_from_map)", "bound": "hbm", "achieved": achieved,
