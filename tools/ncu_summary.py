@@ -20,8 +20,9 @@ METRICS = [
     ("launch__block_size", "block", 1),
     ("smsp__inst_executed.sum", "inst_M", 1e-6),
     ("sm__throughput.avg.pct_of_peak_sustained_elapsed", "sm_%", 1),
-    ("lts__t_sectors_op_atom.sum", "l2_atom_sect_K", 1e-3),
-    ("lts__t_sectors_op_red.sum", "l2_red_sect_K", 1e-3),
+    ("lts__throughput.avg.pct_of_peak_sustained_elapsed", "l2_thr_%", 1),
+    ("l1tex__m_l1tex2xbar_write_sectors_mem_global_op_atom.sum", "atom_sect_K", 1e-3),
+    ("l1tex__m_l1tex2xbar_write_sectors_mem_global_op_red.sum", "red_sect_K", 1e-3),
     ("smsp__average_warp_latency_issue_stalled_long_scoreboard.ratio", "st_long_sb", 1),
     ("smsp__average_warps_issue_stalled_long_scoreboard_per_issue_active.ratio", "st_long_sb", 1),
     ("smsp__average_warps_issue_stalled_lg_throttle_per_issue_active.ratio", "st_lg_thr", 1),
