@@ -13,6 +13,7 @@ _LAZY = {
     "VoxelGenerator": "voxel_generator", "VoxelGenerator_trt": "voxel_generator",
     "decorate": "pillar_ops", "decorate_constants": "pillar_ops", "PointNet": "pillar_ops",
     "PointPillarsScatter": "pillar_ops", "Scatter": "pillar_ops", "Scatter_cuda": "pillar_ops",
+    "AnchorMask": "anchor_mask", "get_anchor_coor": "anchor_mask", "fused_get_anchors_mask_gpu": "anchor_mask",
     "PillarFrontEnd": "frontend", "shard_frames": "sharding", "PillarFrontError": "_lib",
 }
 

@@ -291,4 +291,25 @@ int pf_scatter_backward(const float *grad_canvas, const int32_t *coors, int coor
     return e == cudaSuccess ? PF_OK : cuda_fail(e, "pf_scatter_backward");
 }
 
+int pf_anchor_mask(const int32_t *coors, int coors_stride, const int32_t *voxel_num, int64_t n_rows, int rows_per_frame,
+                   int n_frames, int nx, int ny, const int32_t *anchor_coors, int64_t n_anchors, int32_t *integral,
+                   uint8_t *mask, void *stream)
+{
+    if (n_frames < 0 || n_rows < 0 || n_anchors < 0) return fail(PF_ERR_INVALID_ARGUMENT, "pf_anchor_mask: negative size");
+    if (n_frames == 0) return PF_OK;
+    if (nx < 1 || ny < 1 || (long long)nx * ny >= (1ll << 31)) return fail(PF_ERR_INVALID_ARGUMENT, "pf_anchor_mask: bad grid %d x %d", nx, ny);
+    if (!integral) return fail(PF_ERR_INVALID_ARGUMENT, "pf_anchor_mask: null integral scratch");
+    if (n_rows > 0 && !coors) return fail(PF_ERR_INVALID_ARGUMENT, "pf_anchor_mask: null coors");
+    if (n_anchors > 0 && (!anchor_coors || !mask)) return fail(PF_ERR_INVALID_ARGUMENT, "pf_anchor_mask: null anchor_coors/mask");
+    if (!aligned16(anchor_coors)) return fail(PF_ERR_INVALID_ARGUMENT, "pf_anchor_mask: anchor_coors must be 16-byte aligned");
+    if (coors_stride < 2) return fail(PF_ERR_INVALID_ARGUMENT, "pf_anchor_mask: coors_stride must be >= 2");
+    if (rows_per_frame < 0) return fail(PF_ERR_INVALID_ARGUMENT, "pf_anchor_mask: rows_per_frame < 0");
+    if (rows_per_frame > 0 && !voxel_num) return fail(PF_ERR_INVALID_ARGUMENT, "pf_anchor_mask: the slab layout needs voxel_num");
+    const bool frame_in_column = rows_per_frame == 0 && n_frames > 1;
+    if (frame_in_column && coors_stride < 4) return fail(PF_ERR_INVALID_ARGUMENT, "pf_anchor_mask: frame id is column 3, coors_stride must be >= 4");
+    cudaError_t e = pf::launch_anchor_mask(coors, coors_stride, voxel_num, n_rows, rows_per_frame, n_frames, nx, ny,
+                                           anchor_coors, n_anchors, integral, mask, nullptr, static_cast<cudaStream_t>(stream));
+    return e == cudaSuccess ? PF_OK : cuda_fail(e, "pf_anchor_mask");
+}
+
 }  // extern "C"

@@ -105,6 +105,10 @@ cudaError_t launch_scatter_from_map(const Params &p, const Work &w, const float 
 cudaError_t launch_scatter_backward(const float *grad_canvas, const int32_t *coors, int coors_stride,
                                     int64_t n_voxels, int batch, int n_ch, int nx, int ny, float *grad_feats,
                                     int64_t sv, int64_t sc, cudaStream_t stream);
+cudaError_t launch_anchor_mask(const int32_t *coors, int coors_stride, const int32_t *voxel_num, long long n_rows,
+                               int rows_per_frame, int n_frames, int nx, int ny, const int32_t *anchor_coors,
+                               long long n_anchors, int32_t *integral, uint8_t *mask, int *table_is_u16,
+                               cudaStream_t stream);
 
 // ---- small device helpers -------------------------------------------------------------------------------
 #ifdef __CUDACC__

@@ -123,6 +123,14 @@ class PillarFrontEnd:
             raise ValueError("step needs pillar_feats or pfn")
         return self.scatter(pillar_feats, n_frames)
 
+    def anchor_mask(self, anchors, n_frames=None):
+        """Anchor occupancy mask (n_frames, A) torch.bool of the frames last voxelised, straight from the device
+        coordinates (row N2; ``anchors`` is an anchor_mask.AnchorMask built for this grid)."""
+        n_frames = self.B if n_frames is None else int(n_frames)
+        rows = n_frames * self.max_voxels
+        return anchors.create_mask_batch(self.coors[:rows], self.voxel_num, n_frames,
+                                         0 if self.compact else self.max_voxels)
+
     # ---- CUDA graph of a fixed-shape step --------------------------------------------------------
     def capture(self, points, frame_offsets, pillar_feats):
         """Capture step() for these (static) tensors; replay() re-runs it on whatever they then contain."""

@@ -120,3 +120,33 @@ def make_frame(kind: str, geom: GridGeometry, n: int, seed: int, n_cells: int = 
     if kind == "S4":
         return s4_edges(geom, n, seed, n_cells)
     raise ValueError(f"unknown synthetic frame kind {kind!r}")
+
+
+# sizes (l, w, h) and yaw angles of the anchor set the reference hard-codes (framework/anchor_assigner.py:222-246)
+ANCHOR_CLASSES = (
+    ((4.6, 2.10, 1.8), (0.0, 1.5707963267948966)),
+    ((7.5, 2.6, 2.9), (0.0, 1.5707963267948966)),
+    ((12.6, 2.9, 3.8), (0.0, 1.5707963267948966)),
+    ((0.96874749, 0.9645992, 1.81212425), (0.0,)),
+    ((2.02032733, 0.98075615, 1.72027404), (0.0, 1.5707963267948966)),
+)
+
+
+def anchors_bv(geom: GridGeometry, feature_map=(400, 400), classes=ANCHOR_CLASSES) -> np.ndarray:
+    """Synthetic bird's-eye anchor boxes (A, 4) fp32 = (xmin, ymin, xmax, ymax): one box per feature-map cell, size
+    and yaw, centred on the cell, length and width swapped for the 90-degree yaw.  Same population (9 boxes per
+    feature-map cell = 1.44 M at 400 x 400) as the reference's AnchorAssigner builds at start-up."""
+    fx, fy = int(feature_map[0]), int(feature_map[1])
+    diff = np.asarray(geom.range_diff, np.float32)
+    off = np.asarray(geom.offset, np.float32)
+    sx, sy = diff[0] / np.float32(fx), diff[1] / np.float32(fy)
+    cx = np.arange(fx, dtype=np.float32) * sx + (off[0] + sx / 2)
+    cy = np.arange(fy, dtype=np.float32) * sy + (off[1] + sy / 2)
+    gx, gy = np.meshgrid(cx, cy, indexing="ij")
+    gx, gy = gx.reshape(-1), gy.reshape(-1)
+    out = []
+    for (l, w, _h), yaws in classes:
+        for yaw in yaws:
+            dx, dy = (np.float32(l), np.float32(w)) if abs(yaw) < 0.7 else (np.float32(w), np.float32(l))
+            out.append(np.stack([gx - dx / 2, gy - dy / 2, gx + dx / 2, gy + dy / 2], axis=1))
+    return np.ascontiguousarray(np.concatenate(out, axis=0), np.float32)

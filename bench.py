@@ -45,6 +45,7 @@ def parse_args():
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-single", action="store_true", help="skip the single-frame drop-in latency measurement")
     ap.add_argument("--no-pfn", action="store_true", help="skip the fused-vs-torch PFN side measurement")
+    ap.add_argument("--no-anchor-mask", action="store_true", help="skip the anchor-mask (row N2) side measurement")
     ap.add_argument("--device-pipelines", type=int, default=1,
                     help="device-resident arm: front ends (workspace + graph) in flight; 1 = strictly serial steps (default: the "
                          "fill kernel fills the GPU, so a second batch in flight gains only ~5 %% at 20 cm and loses at 10 cm)")
@@ -315,6 +316,31 @@ def run_b200(args, rank, world, local):
                             "+ ReLU + max in the gather kernel) + fill; torch = CUDA decoration -> pfn_layers in torch -> fill"}
         del net
 
+    # ---------------- next-row N2: anchor occupancy mask of the batch from the device coordinates ------------------
+    anchor = None
+    if rank == 0 and not args.no_anchor_mask:
+        synth = importlib.import_module("3d_object_detection_b200.synth")
+        amod = importlib.import_module("3d_object_detection_b200.anchor_mask")
+        fmap = (int(geom.grid_size[0]) // 2, int(geom.grid_size[1]) // 2)         # feature_map_size of the configs
+        am = amod.AnchorMask(synth.anchors_bv(geom, fmap), voxel_size=np.asarray(cfg["voxel_size"], np.float32),
+                             offset=geom.offset, grid_size=geom.grid_size, device=local)
+        fe.voxelize_decorate(pts_d, offs_d)
+        for _ in range(3):
+            mask_d = fe.anchor_mask(am)
+        torch.cuda.synchronize(dev)
+        a0, a1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        n_am = max(5, min(K, 40))
+        a0.record()
+        for _ in range(n_am):
+            mask_d = fe.anchor_mask(am)
+        a1.record()
+        torch.cuda.synchronize(dev)
+        anchor = {"ms_per_batch": a0.elapsed_time(a1) / n_am, "anchors": am.n_anchors, "frames": B,
+                  "set_fraction": float(mask_d.float().mean().item()),
+                  "note": "pf_anchor_mask on the device coordinates of the batch: memset + count + two parallel scans + "
+                          "four-corner lookup, mask (frames, anchors) bool left on the device"}
+        del am, mask_d
+
     # ---------------- drop-in single-frame latency: the reference's own call sequence (InferData.get + forward) -------
     single = None
     if rank == 0 and not args.no_single:
@@ -396,7 +422,7 @@ def run_b200(args, rank, world, local):
         dist.barrier()
         dist.destroy_process_group()
     return dict(cfg=cfg, geom=geom, frames=frames, B=B, K=K, W=W, t_dev=t_dev, t_e2e=t_e2e, t_vox=t_vox,
-                t_scat=t_scat, with_pfn=with_pfn, single=single, w_e2e=w_e2e, t_serial=t_serial, d_dev=d_dev, counts=counts, bytes_alg=bytes_alg, n_points=n_points, tot_pts=tot_pts,
+                t_scat=t_scat, with_pfn=with_pfn, anchor=anchor, single=single, w_e2e=w_e2e, t_serial=t_serial, d_dev=d_dev, counts=counts, bytes_alg=bytes_alg, n_points=n_points, tot_pts=tot_pts,
                 tot_frames=tot_frames, clocks=clocks, h2d=h2d, d2h=d2h, fe=fe, depth=depth, world=world)
 
 
@@ -461,6 +487,7 @@ def main():
         "stages_ms": {"voxelize_decorate": 1e3 * r["t_vox"], "scatter": 1e3 * r["t_scat"]},
         "bytes_per_step": r["bytes_alg"],
         "with_pfn": r["with_pfn"],
+        "anchor_mask": r["anchor"],
         "single_frame_api": r["single"],
         "e2e_hbm_frac": r["bytes_alg"]["e2e"] / (r["t_dev"] / K) / 1e9 / peak,
         "e2e_hbm_frac_serial": r["bytes_alg"]["e2e"] / (r["t_serial"] / K) / 1e9 / peak,

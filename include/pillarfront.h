@@ -16,6 +16,9 @@
  *   pf_scatter_backward  <-> autograd of the index_put in pointpillars8_shared.py:100 (a gather)
  *   pf_pfn / pf_voxelize_pfn <-> networks/pointpillars8_shared.py:24-28, 57-60 (pfn_layers + max, eval mode), fused
  *                            behind the decoration ("next" row N1)
+ *   pf_anchor_mask       <-> framework/box_np_ops.py:236-257 (fused_get_anchors_mask_gpu = init_map_gpu :168,
+ *                            cumx_gpu :175, cumy_gpu :183, get_anchors_mask_gpu :214), called from
+ *                            AnchorAssigner.create_mask, framework/anchor_assigner.py:322-335 ("next" row N2)
  *
  * Conventions
  *   - plain pointers and sizes only; every pointer named *device* is CUDA device memory on the handle's
@@ -147,6 +150,27 @@ PF_API int pf_scatter_from_map(pf_handle *h, const float *feats, int64_t feat_st
 PF_API int pf_scatter_backward(const float *grad_canvas, const int32_t *coors, int coors_stride, int64_t n_voxels,
                         int batch, int n_ch, int nx, int ny, float *grad_feats, int64_t feat_stride_v,
                         int64_t feat_stride_c, void *stream);
+
+/* Anchor occupancy mask of a batch of frames: mask[f][a] = 1 iff the reference's four-corner sum of the 2-D
+ * running-sum pillar-count table of frame f over anchor rectangle a is > 0.
+ *   coors         device int32 rows (x, y, ...), `coors_stride` ints per row (>= 2)
+ *   voxel_num     device int32 [n_frames] or NULL.
+ *                   NULL                   : rows [0, n_rows) are all valid; their frame is column 3 when
+ *                                            n_frames > 1 (merge_second_batch layout, needs coors_stride >= 4), else 0
+ *                   rows_per_frame  > 0    : slab layout of pf_voxelize (frame f = rows [f*rows_per_frame, +voxel_num[f]))
+ *                   rows_per_frame == 0    : compact layout of pf_voxelize (first sum(voxel_num) rows, frame in column 3)
+ *   n_rows        rows to scan (an upper bound when voxel_num is given)
+ *   anchor_coors  device int32 [n_anchors][4] = (minx, miny, maxx, maxy) from get_anchor_coor
+ *                 (framework/box_np_ops.py:288-304); 16-byte aligned
+ *   integral      device scratch of n_frames * nx * ny * 4 bytes.  Afterwards it holds the running-sum table
+ *                 [n_frames][nx][ny], as uint16 when a frame cannot hold more than 65535 pillars
+ *                 (rows_per_frame, or n_rows when rows_per_frame == 0, is <= 65535), else as int32
+ *   mask          device uint8 [n_frames][n_anchors], 0 / 1 (numpy bool layout)
+ * Pillars with x, y or frame out of range are skipped; a negative corner index counts from the end of its axis
+ * (numpy / numba indexing), one past the end is clamped. */
+PF_API int pf_anchor_mask(const int32_t *coors, int coors_stride, const int32_t *voxel_num, int64_t n_rows,
+                   int rows_per_frame, int n_frames, int nx, int ny, const int32_t *anchor_coors,
+                   int64_t n_anchors, int32_t *integral, uint8_t *mask, void *stream);
 
 #ifdef __cplusplus
 }

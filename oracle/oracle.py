@@ -203,3 +203,33 @@ def pfn(features, weight, gamma, beta, mean, var, eps=1e-5):
     y = (y - np.asarray(mean, np.float64)) / np.sqrt(np.asarray(var, np.float64) + eps) * np.asarray(gamma, np.float64) \
         + np.asarray(beta, np.float64)
     return np.maximum(y, 0.0).max(axis=1)
+
+
+def anchor_coor(anchors_bv, stride, offset, grid_size):
+    """get_anchor_coor, framework/box_np_ops.py:288-304: floor((edge - offset) / stride) in the arrays' own
+    precision, stored as int32, minima clipped at 0 and maxima at grid - 1 (and nothing else)."""
+    bv = np.asarray(anchors_bv)
+    out = np.zeros(bv.shape, dtype=np.int32)
+    for k, axis in enumerate((0, 1, 0, 1)):
+        out[:, k] = np.floor((bv[:, k] - offset[axis]) / stride[axis]).astype(np.int32)
+    out[:, 0] = np.maximum(out[:, 0], 0)
+    out[:, 1] = np.maximum(out[:, 1], 0)
+    out[:, 2] = np.minimum(out[:, 2], grid_size[0] - 1)
+    out[:, 3] = np.minimum(out[:, 3], grid_size[1] - 1)
+    return out
+
+
+def anchors_mask(coors, shape, anchor_coors):
+    """AnchorAssigner.create_mask, framework/anchor_assigner.py:322-335, in the arithmetic both of its branches
+    share: fp32 pillar counts per (x, y) (sparse_sum_for_anchors_mask, box_np_ops.py:160-165 = init_map_gpu
+    :168-172), running sums along axis 0 then axis 1 (cumx_gpu / cumy_gpu :175-188), and the four-corner test of
+    get_anchors_mask_gpu (:214-223) / fused_get_anchors_area (:261-285) on the anchor rectangles."""
+    dense = np.zeros(tuple(int(s) for s in shape), dtype=np.float32)
+    coors = np.asarray(coors)
+    for i in range(coors.shape[0]):
+        dense[coors[i, 0], coors[i, 1]] += 1
+    dense = dense.cumsum(0)
+    dense = dense.cumsum(1)
+    minx, miny, maxx, maxy = (np.asarray(anchor_coors)[:, k] for k in range(4))
+    area = dense[maxx, maxy] - dense[maxx, miny] - dense[minx, maxy] + dense[minx, miny]
+    return area > 0

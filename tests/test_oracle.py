@@ -158,3 +158,35 @@ def test_oracle_vs_parallel_spec_random_geometries():
         assert np.all((c >= 0) & (c < geom.grid_size))
 
     run()
+
+
+@pytest.mark.parametrize("name", util.ANCHOR_NAMES)
+def test_anchor_mask_oracle_matches_reference_golden(name):
+    """Row N2: the restated get_anchor_coor / create_mask arithmetic against vectors made by the reference's own
+    functions (oracle/make_golden_anchor.py)."""
+    g = util.load_anchor(name)
+    ac = oracle.anchor_coor(g["anchors_bv"], g["voxel_size"], g["offset"], g["grid_size"])
+    assert ac.dtype == np.int32 and np.array_equal(ac, g["anchor_coors"])
+    mask = oracle.anchors_mask(g["coors"], g["grid_size"][:2], g["anchor_coors"])
+    assert mask.dtype == np.bool_ and np.array_equal(mask, g["mask"])
+    assert 0 < mask.sum() < mask.size or name == "grid3d"
+
+
+@pytest.mark.parametrize("name", util.ANCHOR_NAMES)
+def test_get_anchor_coor_host_mirror_matches_reference_golden(name):
+    """The product's init-time host function (numpy only, no device work) reproduces the reference's rectangles."""
+    import importlib
+    am = importlib.import_module("3d_object_detection_b200.anchor_mask")
+    g = util.load_anchor(name)
+    got = am.get_anchor_coor(g["anchors_bv"], g["voxel_size"], g["offset"], g["grid_size"])
+    assert got.dtype == np.int32 and np.array_equal(got, g["anchor_coors"])
+
+
+def test_synthetic_anchor_population():
+    """synth.anchors_bv yields the reference's anchor count (9 per feature-map cell) inside the detection range."""
+    geom = cfgmod.derive_grid(cfgmod.builtin_config("20cm"))
+    bv = util.synth.anchors_bv(geom, (40, 40))
+    assert bv.shape == (9 * 1600, 4) and bv.dtype == np.float32
+    assert np.all(bv[:, 2] > bv[:, 0]) and np.all(bv[:, 3] > bv[:, 1])
+    ac = oracle.anchor_coor(bv, geom.voxel_size[:2].astype(np.float32), geom.offset[:2], geom.grid_size)
+    assert ac.min() >= 0 and np.all(ac[:, 2] < geom.grid_size[0]) and np.all(ac[:, 3] < geom.grid_size[1])

@@ -11,6 +11,7 @@ cfgmod = importlib.import_module("3d_object_detection_b200.config")
 synth = importlib.import_module("3d_object_detection_b200.synth")
 
 GRID_KEYS = sorted(cfgmod.GRIDS)
+ANCHOR_NAMES = ["pillar_small", "pillar_sparse", "grid3d"]
 SMALL_NAMES = ["s1", "s1_overflow", "s3_overflow", "s2_ring", "s4_edges", "dense_cap", "n0", "n5"]
 
 
@@ -77,3 +78,8 @@ def load_extra(name):
                max_voxels=int(g["max_voxels"]), max_num_points=int(g["max_points"]),
                num_point_features=int(g["points"].shape[1]), batch_size=1, device=0)
     return g, cfg
+
+
+def load_anchor(name):
+    z = np.load(GOLD / f"anchor_{name}.npz")
+    return {k: z[k] for k in z.files}
