@@ -14,6 +14,7 @@ _LAZY = {
     "decorate": "pillar_ops", "decorate_constants": "pillar_ops", "PointNet": "pillar_ops",
     "PointPillarsScatter": "pillar_ops", "Scatter": "pillar_ops", "Scatter_cuda": "pillar_ops",
     "AnchorMask": "anchor_mask", "get_anchor_coor": "anchor_mask", "fused_get_anchors_mask_gpu": "anchor_mask",
+    "merge_second_batch": "collate", "example_convert_to_torch": "collate",
     "PillarFrontEnd": "frontend", "shard_frames": "sharding", "PillarFrontError": "_lib",
 }
 

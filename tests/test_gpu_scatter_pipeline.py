@@ -216,3 +216,25 @@ def test_pipeline_with_fused_pfn(pf, gkey):
         want_canvas = oracle.scatter(a.cpu().numpy(), coors[:, :3], fe.nx, fe.ny)[0]
         assert np.array_equal(canvas[f].cpu().numpy(), want_canvas)      # the fill itself stays bit-exact
     fe.close()
+
+
+def test_collate_of_device_outputs_equals_generate_batch(pf):
+    """Row N3: merge_second_batch over per-frame device outputs == the collated layout generate_batch writes directly."""
+    import importlib
+    col = importlib.import_module("3d_object_detection_b200.collate")
+    cfg = cfgmod.builtin_config("20cm")
+    cfg["max_voxels"] = 2500
+    geom = cfgmod.derive_grid(cfg)
+    frames = [synth.make_frame(k, geom, 7000, 91 + i) for i, k in enumerate(["S1", "S3", "S2"])]
+    vg = pf.VoxelGenerator(cfg)
+    ex = []
+    for f in frames:
+        v, c, n = vg.generate(f, device_outputs=True)
+        ex.append({"voxels": v.clone(), "coordinates": c.clone(), "num_points_per_voxel": n.clone()})
+    merged = col.merge_second_batch(ex)
+    batch = vg.generate_batch(frames)
+    assert merged["coordinates"].is_cuda and merged["coordinates"].shape[1] == 4
+    for k in ("voxels", "coordinates", "num_points_per_voxel"):
+        assert torch.equal(merged[k], batch[k]), k
+    conv = col.example_convert_to_torch(merged, device=merged["voxels"].device)
+    assert conv["voxels"].data_ptr() == merged["voxels"].data_ptr()          # no copy for resident tensors

@@ -136,3 +136,52 @@ def test_bench_reference_arm_runs_on_cpu():
     line = json.loads([ln for ln in res.stdout.splitlines() if ln.startswith("{")][-1])
     assert line["impl"] == "reference" and line["unit"] == "points/s" and line["value"] > 0
     assert line["cpu_baseline"]["kind"] == "port" and line["e2e"]["h2d_bytes_per_step"] == 0
+
+
+def test_collate_matches_reference_layout():
+    """Row N3: merge_second_batch on numpy examples is the reference's layout (frame id padded as the LAST coordinate
+    column only when the batch has more than one example, framework/utils.py:34-46); torch CPU tensors take the same
+    path the CUDA tensors take."""
+    import importlib
+    torch = pytest.importorskip("torch")
+    col = importlib.import_module("3d_object_detection_b200.collate")
+    rng = np.random.default_rng(3)
+    ex = []
+    for v in (5, 0, 7):
+        ex.append({"voxels": rng.random((v, 4, 4), dtype=np.float32),
+                   "num_points_per_voxel": rng.integers(1, 5, v).astype(np.int32),
+                   "coordinates": rng.integers(0, 50, (v, 3)).astype(np.int32),
+                   "anchors_mask": rng.random(11) > 0.5, "match_indices_num": np.array([v], np.int32),
+                   "image_idx": np.int64(v)})
+    m = col.merge_second_batch(ex)
+    assert m["voxels"].shape == (12, 4, 4) and m["num_points_per_voxel"].shape == (12,)
+    assert m["coordinates"].shape == (12, 4) and m["coordinates"].dtype == np.int32
+    assert np.array_equal(m["coordinates"][:, 3], [0] * 5 + [2] * 7)
+    assert np.array_equal(m["coordinates"][:5, :3], ex[0]["coordinates"])
+    assert m["anchors_mask"].shape == (3, 11) and m["match_indices_num"].tolist() == [5, 0, 7]
+    assert m["image_idx"].tolist() == [5, 0, 7]
+    one = col.merge_second_batch(ex[:1])
+    assert one["coordinates"].shape == (5, 3)                       # no pad for a batch of one
+    # tensors: same values, tensor outputs
+    ext = [{k: (torch.from_numpy(v) if isinstance(v, np.ndarray) and k != "image_idx" else v) for k, v in e.items()}
+           for e in ex]
+    mt = col.merge_second_batch(ext)
+    for k in ("voxels", "num_points_per_voxel", "coordinates", "anchors_mask", "match_indices_num"):
+        assert torch.is_tensor(mt[k]) and np.array_equal(mt[k].numpy(), m[k]), k
+    conv = col.example_convert_to_torch(m, device="cpu")
+    assert conv["voxels"].dtype == torch.float32 and conv["coordinates"].dtype == torch.int32
+    assert conv["anchors_mask"].dtype == torch.bool and conv["image_idx"] is m["image_idx"]
+
+
+def test_collate_matches_reference_golden():
+    """The same function against the output of the reference's own merge_second_batch (oracle/make_golden_collate.py)."""
+    import importlib
+    col = importlib.import_module("3d_object_detection_b200.collate")
+    z = np.load(Path(__file__).resolve().parent / "golden" / "collate.npz")
+    keys = ("voxels", "num_points_per_voxel", "coordinates", "anchors_mask", "match_indices_num")
+    ex = [{k: z[f"in{i}_{k}"] for k in keys} for i in range(3)]
+    for tag, batch in (("merged", ex), ("single", ex[:1])):
+        got = col.merge_second_batch(batch)
+        for k in keys:
+            want = z[f"{tag}_{k}"]
+            assert got[k].dtype == want.dtype and got[k].shape == want.shape and np.array_equal(got[k], want), (tag, k)
