@@ -312,4 +312,28 @@ int pf_anchor_mask(const int32_t *coors, int coors_stride, const int32_t *voxel_
     return e == cudaSuccess ? PF_OK : cuda_fail(e, "pf_anchor_mask");
 }
 
+size_t pf_nms_scratch_bytes(int n_segments, int max_segment_boxes)
+{
+    if (n_segments < 1 || max_segment_boxes < 1 || max_segment_boxes > 4096) return 0;
+    return pf::nms_scratch_bytes(n_segments, max_segment_boxes);
+}
+
+int pf_nms(const float *boxes, const float *scores, const int32_t *seg_offsets, int n_segments, int64_t n_total,
+           int max_segment_boxes, float iou_threshold, int post_max, void *scratch, int32_t *keep, int32_t *keep_num,
+           void *stream)
+{
+    if (n_segments < 0 || n_total < 0) return fail(PF_ERR_INVALID_ARGUMENT, "pf_nms: negative size");
+    if (n_segments == 0) return PF_OK;
+    if (max_segment_boxes < 1 || max_segment_boxes > 4096) return fail(PF_ERR_UNSUPPORTED, "pf_nms: max_segment_boxes %d outside 1..4096", max_segment_boxes);
+    if (post_max < 1) return fail(PF_ERR_INVALID_ARGUMENT, "pf_nms: post_max < 1");
+    if (!seg_offsets && n_segments != 1) return fail(PF_ERR_INVALID_ARGUMENT, "pf_nms: seg_offsets may be null only for one segment");
+    if (!seg_offsets && n_total > max_segment_boxes) return fail(PF_ERR_CAPACITY, "pf_nms: %lld boxes > max_segment_boxes %d", (long long)n_total, max_segment_boxes);
+    if (!scratch || !keep || !keep_num) return fail(PF_ERR_INVALID_ARGUMENT, "pf_nms: null scratch/keep/keep_num");
+    if (n_total > 0 && (!boxes || !scores)) return fail(PF_ERR_INVALID_ARGUMENT, "pf_nms: null boxes/scores");
+    if (!aligned16(boxes) || (reinterpret_cast<uintptr_t>(scratch) & 255)) return fail(PF_ERR_INVALID_ARGUMENT, "pf_nms: boxes must be 16-byte and scratch 256-byte aligned");
+    cudaError_t e = pf::launch_nms(boxes, scores, seg_offsets, n_segments, n_total, max_segment_boxes, iou_threshold, post_max,
+                                   scratch, keep, keep_num, static_cast<cudaStream_t>(stream));
+    return e == cudaSuccess ? PF_OK : cuda_fail(e, "pf_nms");
+}
+
 }  // extern "C"

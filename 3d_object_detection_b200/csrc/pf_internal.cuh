@@ -110,6 +110,11 @@ cudaError_t launch_anchor_mask(const int32_t *coors, int coors_stride, const int
                                long long n_anchors, int32_t *integral, uint8_t *mask, int *table_is_u16,
                                cudaStream_t stream);
 
+size_t nms_scratch_bytes(int n_seg, int max_seg);
+cudaError_t launch_nms(const float *boxes, const float *scores, const int32_t *seg_offsets, int n_seg, long long n_total,
+                       int max_seg, float thresh, int post_max, void *scratch, int32_t *keep, int32_t *keep_num,
+                       cudaStream_t stream);
+
 // ---- small device helpers -------------------------------------------------------------------------------
 #ifdef __CUDACC__
 

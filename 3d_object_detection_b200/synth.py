@@ -150,3 +150,18 @@ def anchors_bv(geom: GridGeometry, feature_map=(400, 400), classes=ANCHOR_CLASSE
             dx, dy = (np.float32(l), np.float32(w)) if abs(yaw) < 0.7 else (np.float32(w), np.float32(l))
             out.append(np.stack([gx - dx / 2, gy - dy / 2, gx + dx / 2, gy + dy / 2], axis=1))
     return np.ascontiguousarray(np.concatenate(out, axis=0), np.float32)
+
+
+def nms_dets(n: int, seed: int) -> np.ndarray:
+    """(n, 5) fp32 detections = standup box (x0, y0, x1, y1) + distinct score: car-sized boxes clustered around a few
+    centres, so that suppression chains occur (input of the NMS row N4)."""
+    rng = np.random.default_rng(seed)
+    k = max(1, n // 6)
+    centres = rng.uniform(-40, 40, (k, 2))
+    c = centres[rng.integers(0, k, n)] + rng.normal(0, 1.2, (n, 2))
+    wh = np.abs(rng.normal([4.5, 2.0], [0.8, 0.4], (n, 2))) + 0.2
+    swap = rng.random(n) < 0.5
+    wh[swap] = wh[swap][:, ::-1]
+    boxes = np.concatenate([c - wh / 2, c + wh / 2], 1)
+    scores = rng.permutation(n).astype(np.float64) / n * 0.9 + 0.05 + rng.uniform(0, 1e-3, n)   # distinct scores
+    return np.concatenate([boxes, scores[:, None]], 1).astype(np.float32)

@@ -19,6 +19,9 @@
  *   pf_anchor_mask       <-> framework/box_np_ops.py:236-257 (fused_get_anchors_mask_gpu = init_map_gpu :168,
  *                            cumx_gpu :175, cumy_gpu :183, get_anchors_mask_gpu :214), called from
  *                            AnchorAssigner.create_mask, framework/anchor_assigner.py:322-335 ("next" row N2)
+ *   pf_nms               <-> framework/nms.py:6-44 (nms_gpu: host argsort, nms_kernel :116-147 with iou_device
+ *                            :102-113, host nms_postprocess :85-99), called through nms(), framework/inference.py:689-703
+ *                            ("next" row N4)
  *
  * Conventions
  *   - plain pointers and sizes only; every pointer named *device* is CUDA device memory on the handle's
@@ -171,6 +174,22 @@ PF_API int pf_scatter_backward(const float *grad_canvas, const int32_t *coors, i
 PF_API int pf_anchor_mask(const int32_t *coors, int coors_stride, const int32_t *voxel_num, int64_t n_rows,
                    int rows_per_frame, int n_frames, int nx, int ny, const int32_t *anchor_coors,
                    int64_t n_anchors, int32_t *integral, uint8_t *mask, void *stream);
+
+/* Standup-box NMS of a batch of independent segments (one per class and frame), entirely on the device.
+ *   boxes         device float [n_total][4] = (x0, y0, x1, y1), 16-byte aligned
+ *   scores        device float [n_total]
+ *   seg_offsets   device int32 [n_segments + 1], or NULL for one segment of n_total boxes
+ *   max_segment_boxes  upper bound on a segment's size, <= 4096 (the reference's pre_max_size is 1000)
+ *   iou_threshold strict `>` test on the reference's IoU (box sides + 1; float64 quotient of float32 differences)
+ *   scratch       device, pf_nms_scratch_bytes(n_segments, max_segment_boxes) bytes, 256-byte aligned
+ *   keep          device int32 [n_segments][post_max]: indices (within the segment) of the kept boxes in
+ *                 descending score order, -1 padded  (= nms(...)[:post_max_size] of the reference)
+ *   keep_num      device int32 [n_segments]: number kept (<= post_max); -1 if the segment exceeded the bound
+ * Equal scores are ordered higher index first (a stable ascending argsort read backwards). */
+PF_API size_t pf_nms_scratch_bytes(int n_segments, int max_segment_boxes);
+PF_API int pf_nms(const float *boxes, const float *scores, const int32_t *seg_offsets, int n_segments, int64_t n_total,
+           int max_segment_boxes, float iou_threshold, int post_max, void *scratch, int32_t *keep,
+           int32_t *keep_num, void *stream);
 
 #ifdef __cplusplus
 }

@@ -233,3 +233,48 @@ def anchors_mask(coors, shape, anchor_coors):
     minx, miny, maxx, maxy = (np.asarray(anchor_coors)[:, k] for k in range(4))
     area = dense[maxx, maxy] - dense[maxx, miny] - dense[minx, maxy] + dense[minx, miny]
     return area > 0
+
+
+def nms_iou_matrix(boxes):
+    """iou_device, framework/nms.py:102-113, for all pairs, in the precision compiled numba gives it: the box edges
+    are float32, `right - left` is a float32 subtraction, and `+ 1` (an int64 literal) promotes everything after it
+    to float64 (numba typing: float32 + int64 -> float64)."""
+    b = np.asarray(boxes, np.float32)
+    x0, y0, x1, y1 = b[:, 0], b[:, 1], b[:, 2], b[:, 3]
+    left = np.maximum(x0[:, None], x0[None, :])
+    right = np.minimum(x1[:, None], x1[None, :])
+    top = np.maximum(y0[:, None], y0[None, :])
+    bottom = np.minimum(y1[:, None], y1[None, :])
+    width = np.maximum((right - left).astype(np.float64) + 1, 0.0)
+    height = np.maximum((bottom - top).astype(np.float64) + 1, 0.0)
+    inter = width * height
+    area = ((x1 - x0).astype(np.float64) + 1) * ((y1 - y0).astype(np.float64) + 1)
+    return inter / (area[:, None] + area[None, :] - inter)
+
+
+def nms_gpu(dets, nms_overlap_thresh):
+    """nms_gpu + nms_kernel + nms_postprocess, framework/nms.py:6-44, 85-147: boxes sorted by descending score, a
+    box is dropped when an earlier KEPT box overlaps it by more than the threshold (strict >).  Returns indices into
+    `dets` in keep order.  Ties in the score are ordered like a stable ascending argsort read backwards."""
+    dets = np.asarray(dets, np.float32)
+    n = dets.shape[0]
+    order = np.argsort(dets[:, 4], kind="stable")[::-1].astype(np.int32)
+    iou = nms_iou_matrix(dets[order, :4])
+    over = iou > np.float64(np.float32(nms_overlap_thresh))
+    removed = np.zeros(n, bool)
+    keep = []
+    for i in range(n):
+        if not removed[i]:
+            keep.append(i)
+            removed[i + 1:] |= over[i, i + 1:]
+    return [int(order[k]) for k in keep]
+
+
+def nms(bboxes, scores, pre_max_size=None, post_max_size=None, iou_threshold=0.5):
+    """nms, framework/inference.py:689-703."""
+    dets = np.concatenate([bboxes, scores[:, np.newaxis]], axis=1)
+    if len(dets) == 0:
+        keep = np.array([], dtype=np.int64)
+    else:
+        keep = np.array(nms_gpu(dets, iou_threshold), dtype=np.int64)[:post_max_size]
+    return None if keep.shape[0] == 0 else keep

@@ -190,3 +190,19 @@ def test_synthetic_anchor_population():
     assert np.all(bv[:, 2] > bv[:, 0]) and np.all(bv[:, 3] > bv[:, 1])
     ac = oracle.anchor_coor(bv, geom.voxel_size[:2].astype(np.float32), geom.offset[:2], geom.grid_size)
     assert ac.min() >= 0 and np.all(ac[:, 2] < geom.grid_size[0]) and np.all(ac[:, 3] < geom.grid_size[1])
+
+
+NMS_CASES = ["n1", "n7", "n64", "n65", "n200", "n300_t5"]
+
+
+@pytest.mark.parametrize("name", NMS_CASES)
+def test_nms_oracle_matches_reference_golden(name):
+    """Row N4: the restated standup-box NMS against the reference's own nms_gpu run under numba's CUDA simulator
+    (oracle/make_golden_nms.py)."""
+    z = np.load(util.GOLD / "nms.npz")
+    dets, thresh, want = z[f"{name}_dets"], z[f"{name}_thresh"], z[f"{name}_keep"]
+    got = oracle.nms_gpu(dets, thresh)
+    assert got == want.tolist()
+    k = oracle.nms(dets[:, :4], dets[:, 4], 1000, 5, thresh)
+    assert k.dtype == np.int64 and k.tolist() == want.tolist()[:5]
+    assert oracle.nms(dets[:0, :4], dets[:0, 4], 1000, 300, thresh) is None
