@@ -46,6 +46,8 @@ def parse_args():
     ap.add_argument("--no-single", action="store_true", help="skip the single-frame drop-in latency measurement")
     ap.add_argument("--no-pfn", action="store_true", help="skip the fused-vs-torch PFN side measurement")
     ap.add_argument("--no-anchor-mask", action="store_true", help="skip the anchor-mask (row N2) side measurement")
+    ap.add_argument("--no-affinity", action="store_true",
+                    help="do not pin the rank to the host cores NVML reports as local to its GPU (NUMA-local pinned buffers)")
     ap.add_argument("--device-pipelines", type=int, default=1,
                     help="device-resident arm: front ends (workspace + graph) in flight; 1 = strictly serial steps (default: the "
                          "fill kernel fills the GPU, so a second batch in flight gains only ~5 %% at 20 cm and loses at 10 cm)")
@@ -76,6 +78,25 @@ def make_batch(pfm, cfg, geom, batch, rank):
     sizes = [len(f) for f in frames]
     offs = np.concatenate([[0], np.cumsum(sizes)]).astype(np.int32)
     return frames, np.concatenate(frames), offs
+
+
+def bind_to_gpu_cores(index):
+    """Best effort: restrict this process to the host cores NVML lists as near GPU `index`, BEFORE the pinned staging
+    buffers are allocated, so that they land on the GPU's NUMA node.  Returns the cores used, or None."""
+    try:
+        import pynvml
+        pynvml.nvmlInit()
+        h = pynvml.nvmlDeviceGetHandleByIndex(index)
+        words = (os.cpu_count() + 63) // 64
+        mask = pynvml.nvmlDeviceGetCpuAffinity(h, words)
+        near = {64 * w + b for w, m in enumerate(mask) for b in range(64) if (m >> b) & 1}
+        cores = sorted(near & os.sched_getaffinity(0))
+        if cores:
+            os.sched_setaffinity(0, cores)
+            return cores
+    except Exception:
+        pass
+    return None
 
 
 class ClockSampler(threading.Thread):
@@ -200,6 +221,7 @@ def run_b200(args, rank, world, local):
         raise SystemExit("bench.py: no CUDA device (the front end has no CPU fallback)")
     torch.cuda.set_device(local)
     dev = torch.device("cuda", local)
+    bound = None if args.no_affinity else bind_to_gpu_cores(local)
     if world > 1:
         dist.init_process_group("nccl", device_id=dev)
 
@@ -422,7 +444,7 @@ def run_b200(args, rank, world, local):
         dist.barrier()
         dist.destroy_process_group()
     return dict(cfg=cfg, geom=geom, frames=frames, B=B, K=K, W=W, t_dev=t_dev, t_e2e=t_e2e, t_vox=t_vox,
-                t_scat=t_scat, with_pfn=with_pfn, anchor=anchor, single=single, w_e2e=w_e2e, t_serial=t_serial, d_dev=d_dev, counts=counts, bytes_alg=bytes_alg, n_points=n_points, tot_pts=tot_pts,
+                t_scat=t_scat, with_pfn=with_pfn, anchor=anchor, single=single, bound=bound, w_e2e=w_e2e, t_serial=t_serial, d_dev=d_dev, counts=counts, bytes_alg=bytes_alg, n_points=n_points, tot_pts=tot_pts,
                 tot_frames=tot_frames, clocks=clocks, h2d=h2d, d2h=d2h, fe=fe, depth=depth, world=world)
 
 
@@ -486,6 +508,7 @@ def main():
         "clocks": r["clocks"],
         "stages_ms": {"voxelize_decorate": 1e3 * r["t_vox"], "scatter": 1e3 * r["t_scat"]},
         "bytes_per_step": r["bytes_alg"],
+        "host_binding": {"cores": len(r["bound"]), "first": r["bound"][0], "last": r["bound"][-1]} if r["bound"] else None,
         "with_pfn": r["with_pfn"],
         "anchor_mask": r["anchor"],
         "single_frame_api": r["single"],
