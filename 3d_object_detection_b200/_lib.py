@@ -11,7 +11,8 @@ LIB_PATH = Path(__file__).resolve().parent / "lib" / "libpillarfront.so"
 
 EXPORTS = ["pf_version", "pf_last_error_string", "pf_create", "pf_destroy", "pf_workspace_bytes",
            "pf_voxelize", "pf_voxelize_decorate", "pf_voxelize_pfn", "pf_pfn", "pf_decorate", "pf_scatter", "pf_scatter_from_map",
-           "pf_scatter_backward", "pf_anchor_mask", "pf_nms", "pf_nms_scratch_bytes"]
+           "pf_scatter_backward", "pf_anchor_mask", "pf_nms", "pf_nms_scratch_bytes",
+           "pf_debug_stage_timing", "pf_debug_stage_times"]
 
 
 class GridDesc(C.Structure):
@@ -73,6 +74,10 @@ def load():
                                       C.c_int64, C.c_int64, _p]
     L.pf_anchor_mask.restype = C.c_int
     L.pf_anchor_mask.argtypes = [_p, C.c_int, _p, C.c_int64, C.c_int, C.c_int, C.c_int, C.c_int, _p, C.c_int64, _p, _p, _p]
+    L.pf_debug_stage_timing.restype = C.c_int
+    L.pf_debug_stage_timing.argtypes = [_p, C.c_int]
+    L.pf_debug_stage_times.restype = C.c_int
+    L.pf_debug_stage_times.argtypes = [_p, C.POINTER(C.c_float), C.c_int]
     L.pf_nms_scratch_bytes.restype = C.c_size_t
     L.pf_nms_scratch_bytes.argtypes = [C.c_int, C.c_int]
     L.pf_nms.restype = C.c_int

@@ -16,6 +16,8 @@ struct pf_handle {
     int max_points_per_frame;
     size_t bytes;
     void *slab;   // one allocation, carved into the Work arrays
+    cudaEvent_t events[pf::kStageEvents];
+    bool timing;
 };
 
 namespace {
@@ -147,12 +149,45 @@ int pf_destroy(pf_handle *h)
 {
     if (!h) return PF_OK;
     DeviceGuard guard(h->device);
+    if (h->timing)
+        for (auto &ev : h->events) cudaEventDestroy(ev);
     cudaError_t e = cudaFree(h->slab);
     delete h;
     return e == cudaSuccess ? PF_OK : cuda_fail(e, "pf_destroy: cudaFree");
 }
 
 size_t pf_workspace_bytes(const pf_handle *h) { return h ? h->bytes : 0; }
+
+int pf_debug_stage_timing(pf_handle *h, int enable)
+{
+    if (!h) return fail(PF_ERR_INVALID_ARGUMENT, "pf_debug_stage_timing: null handle");
+    DeviceGuard guard(h->device);
+    if (enable && !h->timing) {
+        for (auto &ev : h->events) {
+            cudaError_t e = cudaEventCreate(&ev);
+            if (e != cudaSuccess) return cuda_fail(e, "pf_debug_stage_timing: cudaEventCreate");
+        }
+        h->timing = true;
+    }
+    h->w.ev = (enable && h->timing) ? h->events : nullptr;
+    return PF_OK;
+}
+
+int pf_debug_stage_times(pf_handle *h, float *ms, int capacity)
+{
+    if (!h || !ms) return fail(PF_ERR_INVALID_ARGUMENT, "pf_debug_stage_times: null argument");
+    if (!h->w.ev) return fail(PF_ERR_INVALID_ARGUMENT, "pf_debug_stage_times: timing is not enabled");
+    if (capacity < pf::kStageEvents - 1) return fail(PF_ERR_CAPACITY, "pf_debug_stage_times: need room for %d values", pf::kStageEvents - 1);
+    DeviceGuard guard(h->device);
+    for (int k = 1; k < pf::kStageEvents; ++k) {
+        ms[k - 1] = -1.f;
+        if (cudaEventSynchronize(h->events[k]) != cudaSuccess || cudaEventElapsedTime(&ms[k - 1], h->events[k - 1], h->events[k]) != cudaSuccess) {
+            cudaGetLastError();   // a stage that did not run in the last call
+            ms[k - 1] = -1.f;
+        }
+    }
+    return pf::kStageEvents - 1;
+}
 
 static int voxelize_common(pf_handle *h, const pf::VoxelizeArgs &a, void *stream, const char *who)
 {

@@ -43,7 +43,13 @@ struct Work {
     int32_t *istar;     // [B] cut-off index i*: first point index the sequential loop never reaches
     int32_t *vnum;      // [B] voxels per frame
     int32_t *map;       // [B][plane] cell -> feature row for the stand-alone scatter, -1 = none
+    cudaEvent_t *ev;    // host array of kStageEvents events, or nullptr: per-kernel timing (pf_debug_stage_timing)
 };
+
+// stage boundaries recorded when Work::ev is set (eager launches only; not capturable into a graph)
+enum Stage { kEvStart = 0, kEvQuantize, kEvAssign, kEvTileRank, kEvColumnScan, kEvSlot, kEvGather, kEvFillStart, kEvFill,
+             kStageEvents };
+inline void mark(const Work &w, int k, cudaStream_t s) { if (w.ev) cudaEventRecord(w.ev[k], s); }
 
 struct VoxelizeArgs {
     const float *points;

@@ -235,7 +235,10 @@ cudaError_t launch_scatter(const Params &p, const Work &w, const float *feats, i
 cudaError_t launch_scatter_from_map(const Params &p, const Work &w, const float *feats, int64_t sv, int64_t sc,
                                     int n_frames, int compact, int n_ch, float *canvas, cudaStream_t stream)
 {
-    return run_fill<1>(w.grid, feats, sv, sc, w.vnum, p.max_voxels, compact, n_frames, n_ch, p.plane, canvas, stream);
+    mark(w, kEvFillStart, stream);
+    const cudaError_t e = run_fill<1>(w.grid, feats, sv, sc, w.vnum, p.max_voxels, compact, n_frames, n_ch, p.plane, canvas, stream);
+    mark(w, kEvFill, stream);
+    return e;
 }
 
 cudaError_t launch_scatter_backward(const float *grad_canvas, const int32_t *coors, int coors_stride,

@@ -553,6 +553,7 @@ cudaError_t launch_voxelize(const Params &p, const Work &w, const VoxelizeArgs &
     const dim3 g_pts((npts + kPtsPerCta - 1) / kPtsPerCta, B), g_tiles(tiles, B);
     // leading 1/16 of every frame first (see k_quantize); small frames go in one launch
     const int split = npts >= 32 * kPtsPerCta ? ((npts / 16 + kPtsPerCta - 1) / kPtsPerCta) * kPtsPerCta : npts;
+    mark(w, kEvStart, stream);
     for (int pass = 0; pass < 2; ++pass) {
         const int lo = pass == 0 ? 0 : split, hi = pass == 0 ? split : npts;
         if (lo >= hi) continue;
@@ -560,14 +561,19 @@ cudaError_t launch_voxelize(const Params &p, const Work &w, const VoxelizeArgs &
         if (vec4) k_quantize<true><<<g, 256, 0, stream>>>(p, w, a.points, a.frame_offsets, a.point_stride, lo, hi);
         else      k_quantize<false><<<g, 256, 0, stream>>>(p, w, a.points, a.frame_offsets, a.point_stride, lo, hi);
     }
+    mark(w, kEvQuantize, stream);
     k_assign<<<g_tiles, 256, 0, stream>>>(p, w, a.frame_offsets, a.voxel_num);
+    mark(w, kEvAssign, stream);
     if ((size_t)p.vcols > 48 * 1024) {
         cudaError_t e = cudaFuncSetAttribute(k_tile_rank, cudaFuncAttributeMaxDynamicSharedMemorySize, p.vcols);
         if (e != cudaSuccess) return e;
     }
     k_tile_rank<<<g_tiles, kTileWarps * 32, p.vcols, stream>>>(p, w, a.frame_offsets);
+    mark(w, kEvTileRank, stream);
     k_column_scan<<<dim3((p.vcols / 4 + 127) / 128, B), 128, 0, stream>>>(p, w, a.frame_offsets);
+    mark(w, kEvColumnScan, stream);
     k_slot<<<g_pts, 256, 0, stream>>>(p, w, a.frame_offsets, a.keep_cell_map ? 0 : 1);
+    mark(w, kEvSlot, stream);
 
     GatherArgs ga{};
     ga.points = a.points, ga.frame_offsets = a.frame_offsets, ga.point_stride = a.point_stride;
@@ -581,6 +587,7 @@ cudaError_t launch_voxelize(const Params &p, const Work &w, const VoxelizeArgs &
         e = dispatch_gather<true>(p, w, ga, dim3((p.max_voxels + 15) / 16, B), dim3((p.max_voxels + 7) / 8, B), vec4,
                                   stream);
     if (e != cudaSuccess) return e;
+    mark(w, kEvGather, stream);
     return cudaGetLastError();
 }
 

@@ -80,6 +80,13 @@ PF_API int pf_create(const pf_grid_desc *desc, int max_frames, int max_points_pe
 PF_API int pf_destroy(pf_handle *h);
 PF_API size_t pf_workspace_bytes(const pf_handle *h);
 
+/* Diagnostics: with timing enabled every voxelise / fill call of this handle records a CUDA event after each of
+ * its kernels (eager launches only -- do not capture such a call into a graph).  pf_debug_stage_times waits for
+ * the last call and writes the 8 stage durations in milliseconds (quantize, assign, tile_rank, column_scan, slot,
+ * gather, gap between gather and fill, canvas fill; -1 for a stage that did not run); returns the count. */
+PF_API int pf_debug_stage_timing(pf_handle *h, int enable);
+PF_API int pf_debug_stage_times(pf_handle *h, float *ms, int capacity);
+
 /* Output layouts (both written densely, padding rows zeroed):
  *   slab    (compact == 0): frame f owns rows [f*max_voxels, f*max_voxels + voxel_num[f]) of every output;
  *   compact (compact != 0): frames are concatenated, frame f starts at row sum(voxel_num[0..f)), exactly what
