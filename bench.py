@@ -62,6 +62,16 @@ def dist_env():
     return rank, world, local
 
 
+def spread_device(local, world, n_visible):
+    """GPU for local rank `local` when fewer ranks than GPUs run: alternate between the two halves of the box
+    (0, n/2, 1, n/2+1, ...) so that 2 or 4 ranks do not all hang off the same host bridge (PF_DEVICE_MAP=linear keeps
+    LOCAL_RANK -> GPU)."""
+    if os.environ.get("PF_DEVICE_MAP", "spread") == "linear" or world >= n_visible or n_visible % 2:
+        return local
+    half = n_visible // 2
+    return (local % 2) * half + local // 2
+
+
 def make_batch(pfm, cfg, geom, batch, rank):
     """B seeded frames for this rank (kinds cycle S1,S2,S3), concatenated, + int32 offsets."""
     synth = importlib.import_module("3d_object_detection_b200.synth")
@@ -219,6 +229,7 @@ def run_b200(args, rank, world, local):
     pfm = importlib.import_module("3d_object_detection_b200")
     if not torch.cuda.is_available():
         raise SystemExit("bench.py: no CUDA device (the front end has no CPU fallback)")
+    local = spread_device(local, world, torch.cuda.device_count())
     torch.cuda.set_device(local)
     dev = torch.device("cuda", local)
     bound = None if args.no_affinity else bind_to_gpu_cores(local)
@@ -508,6 +519,7 @@ def main():
         "clocks": r["clocks"],
         "stages_ms": {"voxelize_decorate": 1e3 * r["t_vox"], "scatter": 1e3 * r["t_scat"]},
         "bytes_per_step": r["bytes_alg"],
+        "device_of_rank0": r["fe"].device.index,
         "host_binding": {"cores": len(r["bound"]), "first": r["bound"][0], "last": r["bound"][-1]} if r["bound"] else None,
         "with_pfn": r["with_pfn"],
         "anchor_mask": r["anchor"],
