@@ -75,6 +75,57 @@ def test_no_cpu_fallback(pf):
         pf.decorate(torch.zeros(2, 3, 4), torch.ones(2, dtype=torch.int32), torch.zeros(2, 3, dtype=torch.int32), .2, .2, 0., 0.)
 
 
+def test_no_cpu_fallback_next_rows(pf):
+    """Anchor mask and NMS (rows N2 / N4) also refuse to run without a device."""
+    import importlib
+    import torch
+    if torch.cuda.is_available():
+        pytest.skip("GPU present")
+    am = importlib.import_module("3d_object_detection_b200.anchor_mask")
+    nm = importlib.import_module("3d_object_detection_b200.nms")
+    with pytest.raises(pf.PillarFrontError):
+        am.AnchorMask(np.zeros((4, 4), np.float32), voxel_size=np.float32([.2, .2, 11]), offset=np.float32([0, 0, 0]),
+                      grid_size=np.array([8, 8, 1]))
+    with pytest.raises(pf.PillarFrontError):
+        nm.nms_gpu(np.zeros((3, 5), np.float32), 0.1)
+    with pytest.raises(pf.PillarFrontError):
+        nm.nms(np.zeros((3, 4), np.float32), np.zeros(3, np.float32), 1000, 300, 0.1)
+
+
+def test_c_abi_argument_validation_needs_no_device():
+    """Bad arguments are rejected with a negative pf_status and a message before any CUDA call is made."""
+    L = importlib.import_module("3d_object_detection_b200._lib").load()
+    one = ctypes.c_void_p(256)      # non-null, aligned, never dereferenced: validation fails first
+    cases = [
+        (L.pf_anchor_mask(one, 1, None, 5, 0, 1, 8, 8, one, 3, one, one, None), "coors_stride"),
+        (L.pf_anchor_mask(one, 3, None, 5, 0, 2, 8, 8, one, 3, one, one, None), "column 3"),
+        (L.pf_anchor_mask(one, 4, None, 5, 7, 2, 8, 8, one, 3, one, one, None), "voxel_num"),
+        (L.pf_anchor_mask(one, 3, None, 5, 0, 1, 0, 8, one, 3, one, one, None), "grid"),
+        (L.pf_anchor_mask(one, 3, None, 5, 0, 1, 8, 8, ctypes.c_void_p(260), 3, one, one, None), "aligned"),
+        (L.pf_nms(one, one, None, 1, 5, 5000, 0.1, 10, one, one, one, None), "max_segment_boxes"),
+        (L.pf_nms(one, one, None, 2, 5, 100, 0.1, 10, one, one, one, None), "seg_offsets"),
+        (L.pf_nms(one, one, None, 1, 500, 100, 0.1, 10, one, one, one, None), "max_segment_boxes"),
+        (L.pf_nms(one, one, None, 1, 5, 100, 0.1, 0, one, one, one, None), "post_max"),
+        (L.pf_nms(one, one, None, 1, 5, 100, 0.1, 10, None, one, one, None), "scratch"),
+        (L.pf_voxelize(None, one, one, 1, 5, 4, 0, 3, one, one, one, one, None), "null handle"),
+        (L.pf_pfn(one, one, one, 3, 5, 15, 4, .2, .2, 0., 0., one, one, one, 32, one, None), "n_ch"),
+        (L.pf_decorate(one, one, one, 1, 5, 15, 4, .2, .2, 0., 0., one, None), "coors_stride"),
+        (L.pf_scatter_backward(one, one, 3, 5, 0, 64, 8, 8, one, 64, 1, None), "bad sizes"),
+    ]
+    for rc, needle in cases:
+        assert rc < 0, needle
+    # the message belongs to the last failing call of this thread
+    assert L.pf_scatter_backward(one, one, 3, 5, 0, 64, 8, 8, one, 64, 1, None) < 0
+    assert b"bad sizes" in L.pf_last_error_string()
+    assert L.pf_nms(one, one, None, 1, 5, 5000, 0.1, 10, one, one, one, None) < 0
+    assert b"max_segment_boxes" in L.pf_last_error_string()
+    assert L.pf_nms_scratch_bytes(0, 100) == 0 and L.pf_nms_scratch_bytes(1, 5000) == 0
+    assert L.pf_nms_scratch_bytes(24, 1000) >= 24 * 1000 * (16 + 4 + 16 * 8)
+    # empty work is accepted without a device
+    assert L.pf_nms(None, None, None, 0, 0, 100, 0.1, 10, None, None, None, None) == 0
+    assert L.pf_anchor_mask(None, 3, None, 0, 0, 0, 8, 8, None, 0, None, None, None) == 0
+
+
 def test_product_never_imports_oracle():
     for path in (ROOT / "3d_object_detection_b200").rglob("*.py"):
         text = path.read_text()
