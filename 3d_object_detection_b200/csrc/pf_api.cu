@@ -109,6 +109,8 @@ int pf_create(const pf_grid_desc *d, int max_frames, int max_points_per_frame, i
     p.vcols = (int)align_up((size_t)d->max_voxels, 16);
     p.ny_m = (unsigned)((1ull << 32) / (unsigned)p.ny);   // ny, nz == 1 are short-cut in div_small
     p.nz_m = (unsigned)((1ull << 32) / (unsigned)p.nz);
+    p.vbits = 0;
+    while ((1 << p.vbits) < d->max_voxels) ++p.vbits;
     if ((size_t)p.vcols > 200 * 1024) { delete h; return fail(PF_ERR_UNSUPPORTED, "pf_create: max_voxels %d too large for the tile table", d->max_voxels); }
 
     const size_t B = (size_t)max_frames;

@@ -28,6 +28,7 @@ struct Params {
     int tiles_cap;    // npts_cap / kTile
     int vcols;        // row stride of the count matrix (max_voxels rounded up to 16)
     unsigned ny_m, nz_m;   // floor(2^32 / ny), floor(2^32 / nz): magic multipliers of div_small()
+    int vbits;        // bits needed for a voxel id: smallest b with 2^b >= max_voxels
 };
 
 // Device scratch owned by a handle.  Nothing here is API-visible; none of it counts as algorithmic bytes.

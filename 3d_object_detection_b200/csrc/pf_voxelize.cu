@@ -214,7 +214,7 @@ __global__ void __launch_bounds__(256) k_assign(Params p, Work w, const int32_t 
 // ---------------------------------------------------------------------------------------------------------
 // K4: in-tile ranks.  A tile is kTile consecutive points; warp w owns points [w*256, (w+1)*256) of the tile
 // and walks them in kTileSteps steps of 32, so (warp, step, lane) order == point order.  Lanes of one step
-// that fall in the same voxel are grouped with match.any; the group's lowest lane bumps the voxel's byte
+// that fall in the same voxel are grouped (ballots over the id bits); the group's lowest lane bumps the voxel's byte
 // counter in shared memory and the group derives its ranks from the old value.  Warps take turns (warp 0
 // first) so counters are bumped in point order without atomics.  Result: vr[i] = (voxel << 8 | rank in
 // tile) and one row of the (tile x voxel) count matrix, written densely so the matrix never needs clearing.
@@ -249,10 +249,19 @@ __global__ void __launch_bounds__(kTileWarps * 32) k_tile_rank(Params p, Work w,
         const int c = vid[s];
         vid[s] = (c >= 0) ? ~grid[c] : -1;   // every inside point below i* sits in a cell that owns a voxel
     }
+    // Lanes of a step with the same voxel: one ballot per bit of the voxel id, each lane keeps the lanes that agree
+    // with it on every bit.  (match.any does this in one instruction, but its cost grows with the number of distinct
+    // keys -- ~330 cycles for 32 different voxels -- and it was half of this kernel's time; vbits ballots are ~60.)
 #pragma unroll
     for (int s = 0; s < kTileSteps; ++s) {
-        const unsigned key = vid[s] >= 0 ? (unsigned)vid[s] : (0x40000000u | (unsigned)lane);
-        grp[s] = __match_any_sync(0xffffffffu, key);
+        const bool ok = vid[s] >= 0;
+        unsigned m = __ballot_sync(0xffffffffu, ok);
+        for (int b = 0; b < p.vbits; ++b) {
+            const bool one = (vid[s] >> b) & 1;
+            const unsigned bal = __ballot_sync(0xffffffffu, one);
+            m &= one ? bal : ~bal;
+        }
+        grp[s] = ok ? m : (1u << lane);
     }
     __syncthreads();   // table zeroed
 
