@@ -43,7 +43,8 @@ def build(force: bool = False, verbose: bool = False) -> Path:
         return LIB
     LIB_DIR.mkdir(exist_ok=True)
     tmp = LIB.with_suffix(".so.tmp")
-    cmd = [nvcc_path(), *NVCC_FLAGS, "-I", str(ROOT / "include"), "-I", str(CSRC),
+    extra = os.environ.get("PF_NVCC_EXTRA", "").split()      # experiments only, e.g. PF_NVCC_EXTRA=-DPF_TR_MINB=4
+    cmd = [nvcc_path(), *NVCC_FLAGS, *extra, "-I", str(ROOT / "include"), "-I", str(CSRC),
            "-o", str(tmp)] + [str(CSRC / s) for s in SOURCES]
     res = subprocess.run(cmd, capture_output=True, text=True)
     (LIB_DIR / "build.log").write_text("$ " + " ".join(cmd) + "\n" + res.stdout + res.stderr)
