@@ -169,7 +169,8 @@ __global__ void __launch_bounds__(256) k_assign(Params p, Work w, const int32_t 
             while (!done) {
                 unsigned st = 2u << 30;   // "before tile 0": inclusive prefix 0
                 if (j >= 0) {
-                    do { st = ld_status(status + j); } while ((st >> 30) == 0u);
+                    // back off between polls: hundreds of warps spin on the lines their predecessors must write
+                    while (((st = ld_status(status + j)) >> 30) == 0u) __nanosleep(50);
                 }
                 const unsigned inc_mask = __ballot_sync(0xffffffffu, (st >> 30) == 2u);
                 int val = (int)(st & 0x3fffffffu);
