@@ -132,19 +132,21 @@ class PillarFrontEnd:
                                          0 if self.compact else self.max_voxels)
 
     # ---- CUDA graph of a fixed-shape step --------------------------------------------------------
-    def capture(self, points, frame_offsets, pillar_feats):
-        """Capture step() for these (static) tensors; replay() re-runs it on whatever they then contain."""
-        self._g_inputs = (points, frame_offsets, pillar_feats)
+    def capture(self, points, frame_offsets, pillar_feats=None, pfn=None):
+        """Capture step() for these (static) tensors; replay() re-runs it on whatever they then contain.  With ``pfn``
+        (a PointNet in eval mode) the fused voxelise + decorate + PFN kernel is captured; its folded weights are
+        read at capture time."""
+        self._g_inputs = (points, frame_offsets, pillar_feats, pfn)
         side = torch.cuda.Stream(self.device)
         side.wait_stream(torch.cuda.current_stream(self.device))
-        with torch.cuda.stream(side):
+        with torch.cuda.stream(side), torch.no_grad():
             for _ in range(2):
-                self.step(points, frame_offsets, pillar_feats)
+                self.step(points, frame_offsets, pillar_feats=pillar_feats, pfn=pfn)
         torch.cuda.current_stream(self.device).wait_stream(side)
         torch.cuda.synchronize(self.device)
         g = torch.cuda.CUDAGraph()
-        with torch.cuda.graph(g):
-            self.step(points, frame_offsets, pillar_feats)
+        with torch.cuda.graph(g), torch.no_grad():
+            self.step(points, frame_offsets, pillar_feats=pillar_feats, pfn=pfn)
         self._graph = g
         return g
 

@@ -215,6 +215,19 @@ def test_pipeline_with_fused_pfn(pf, gkey):
         coors = fe.coors[lo:lo + counts[f]].cpu().numpy()
         want_canvas = oracle.scatter(a.cpu().numpy(), coors[:, :3], fe.nx, fe.ny)[0]
         assert np.array_equal(canvas[f].cpu().numpy(), want_canvas)      # the fill itself stays bit-exact
+    # the same step captured into a CUDA graph, without materialising voxels / decorated rows, on new contents
+    fe2 = pf.PillarFrontEnd(cfg, max_batch=3, max_points_per_frame=9000, device=0, want_voxels=False)
+    pts2 = torch.zeros_like(pts)
+    fe2.capture(pts2, offs, pfn=net)
+    pts2.copy_(pts)
+    for rep in range(2):
+        got = fe2.replay()
+        assert torch.equal(got, canvas), f"graph replay {rep}"
+        assert torch.equal(fe2.voxel_num, fe.voxel_num)
+        for f in range(3):
+            sl = slice(f * cfg["max_voxels"], f * cfg["max_voxels"] + int(counts[f]))
+            assert torch.equal(fe2.pillar_feats[sl], fused_rows[sl])
+    fe2.close()
     fe.close()
 
 
