@@ -236,3 +236,24 @@ def test_collate_matches_reference_golden():
         for k in keys:
             want = z[f"{tag}_{k}"]
             assert got[k].dtype == want.dtype and got[k].shape == want.shape and np.array_equal(got[k], want), (tag, k)
+
+
+def test_bench_rank_placement():
+    """bench.spread_device: fewer ranks than GPUs alternate between the two halves of the box; a full box, an odd
+    box, or PF_DEVICE_MAP=linear keep LOCAL_RANK -> GPU."""
+    import os
+    bench = importlib.import_module("bench")
+    old = os.environ.pop("PF_DEVICE_MAP", None)
+    try:
+        assert [bench.spread_device(r, 4, 8) for r in range(4)] == [0, 4, 1, 5]
+        assert [bench.spread_device(r, 2, 8) for r in range(2)] == [0, 4]
+        assert [bench.spread_device(r, 8, 8) for r in range(8)] == list(range(8))
+        assert [bench.spread_device(r, 2, 4) for r in range(2)] == [0, 2]
+        assert bench.spread_device(0, 1, 8) == 0 and bench.spread_device(1, 2, 3) == 1
+        assert sorted(bench.spread_device(r, 6, 8) for r in range(6)) == [0, 1, 2, 4, 5, 6]     # a permutation, no clash
+        os.environ["PF_DEVICE_MAP"] = "linear"
+        assert [bench.spread_device(r, 4, 8) for r in range(4)] == [0, 1, 2, 3]
+    finally:
+        os.environ.pop("PF_DEVICE_MAP", None)
+        if old is not None:
+            os.environ["PF_DEVICE_MAP"] = old
