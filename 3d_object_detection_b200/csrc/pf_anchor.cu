@@ -97,19 +97,22 @@ k_am_scan_y(T *__restrict__ integ, long long n_rows, int ny)
     }
 }
 
-// cumx_gpu: running sum along x (stride ny).  One CTA per (32-column strip, frame); its 32 warps split the rows,
-// sum their slice, exchange the 32 x 32 slice totals through shared memory, then rewrite their slice.
+// cumx_gpu: running sum along x (stride ny).  One CTA per (32-column strip, frame); its 16 warps split the rows,
+// sum their slice, exchange the 16 x 32 slice totals through shared memory, then rewrite their slice.  (512 threads:
+// three CTAs fit an SM, so the 200 strips of a 20 cm batch run in one wave; 1024-thread CTAs needed two.)
+constexpr int kAmScanWarps = 16;
+
 template <typename T>
-__global__ void __launch_bounds__(1024)
+__global__ void __launch_bounds__(kAmScanWarps * 32)
 k_am_scan_x(T *__restrict__ integ, int nx, int ny)
 {
-    __shared__ int s_part[32][33];
+    __shared__ int s_part[kAmScanWarps][33];
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     const int col = blockIdx.x * 32 + lane;
     const bool ok = col < ny;
     T *p = integ + (size_t)blockIdx.y * nx * ny + col;
-    const int per = (nx + 31) / 32;
-    const int r0 = warp * per, r1 = min(nx, r0 + per);
+    const int per = (nx + kAmScanWarps - 1) / kAmScanWarps;
+    const int r0 = min(nx, warp * per), r1 = min(nx, r0 + per);
     int sum = 0;
     if (ok)
         for (int r = r0; r < r1; ++r) sum += p[(size_t)r * ny];
@@ -173,7 +176,7 @@ cudaError_t run_anchor_mask(const int32_t *coors, int coors_stride, const int32_
     }
     const long long rows = (long long)n_frames * nx;
     k_am_scan_y<T><<<(unsigned)((rows * 32 + kAmThreads - 1) / kAmThreads), kAmThreads, 0, stream>>>(table, rows, ny);
-    k_am_scan_x<T><<<dim3((unsigned)((ny + 31) / 32), (unsigned)n_frames), 1024, 0, stream>>>(table, nx, ny);
+    k_am_scan_x<T><<<dim3((unsigned)((ny + 31) / 32), (unsigned)n_frames), kAmScanWarps * 32, 0, stream>>>(table, nx, ny);
     if (n_anchors > 0) {
         const dim3 grid((unsigned)((n_anchors + kAmThreads - 1) / kAmThreads),
                         (unsigned)((n_frames + kAmFrameGroup - 1) / kAmFrameGroup));
