@@ -97,15 +97,15 @@ k_am_scan_y(T *__restrict__ integ, long long n_rows, int ny)
     }
 }
 
-// cumx_gpu: running sum along x (stride ny).  One CTA per (32-column strip, frame); its 16 warps split the rows,
-// sum their slice, exchange the 16 x 32 slice totals through shared memory, then rewrite their slice.  (512 threads:
-// three CTAs fit an SM, so the 200 strips of a 20 cm batch run in one wave; 1024-thread CTAs needed two.)
-constexpr int kAmScanWarps = 16;
-
-template <typename T>
-__global__ void __launch_bounds__(kAmScanWarps * 32)
+// cumx_gpu: running sum along x (stride ny).  One CTA per (32-column strip, frame); its WARPS warps split the rows,
+// sum their slice, exchange the WARPS x 32 slice totals through shared memory, then rewrite their slice.  32 warps
+// give the shortest row walk per warp (small batches: 58 vs 65 us for the whole mask at 20 cm x 8 frames); 16 warps
+// let three CTAs share an SM, which wins once there are several waves of strips (10 cm x 32 frames: 0.68 vs 0.73 ms).
+template <typename T, int WARPS>
+__global__ void __launch_bounds__(WARPS * 32)
 k_am_scan_x(T *__restrict__ integ, int nx, int ny)
 {
+    constexpr int kAmScanWarps = WARPS;
     __shared__ int s_part[kAmScanWarps][33];
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     const int col = blockIdx.x * 32 + lane;
@@ -176,7 +176,11 @@ cudaError_t run_anchor_mask(const int32_t *coors, int coors_stride, const int32_
     }
     const long long rows = (long long)n_frames * nx;
     k_am_scan_y<T><<<(unsigned)((rows * 32 + kAmThreads - 1) / kAmThreads), kAmThreads, 0, stream>>>(table, rows, ny);
-    k_am_scan_x<T><<<dim3((unsigned)((ny + 31) / 32), (unsigned)n_frames), kAmScanWarps * 32, 0, stream>>>(table, nx, ny);
+    const dim3 g_strips((unsigned)((ny + 31) / 32), (unsigned)n_frames);
+    if ((long long)g_strips.x * g_strips.y >= 2 * 148)
+        k_am_scan_x<T, 16><<<g_strips, 16 * 32, 0, stream>>>(table, nx, ny);
+    else
+        k_am_scan_x<T, 32><<<g_strips, 32 * 32, 0, stream>>>(table, nx, ny);
     if (n_anchors > 0) {
         const dim3 grid((unsigned)((n_anchors + kAmThreads - 1) / kAmThreads),
                         (unsigned)((n_frames + kAmFrameGroup - 1) / kAmFrameGroup));
