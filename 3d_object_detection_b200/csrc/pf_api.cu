@@ -18,6 +18,7 @@ struct pf_handle {
     void *slab;   // one allocation, carved into the Work arrays
     cudaEvent_t events[pf::kStageEvents];
     bool timing;
+    int map_pending;   // frames whose grid still holds the cell -> voxel map of a keep_cell_map call
 };
 
 namespace {
@@ -206,9 +207,14 @@ static int voxelize_common(pf_handle *h, const pf::VoxelizeArgs &a, void *stream
     if (a.voxels && !aligned16(a.voxels)) return fail(PF_ERR_INVALID_ARGUMENT, "%s: voxels must be 16-byte aligned", who);
     if (a.features && !aligned16(a.features)) return fail(PF_ERR_INVALID_ARGUMENT, "%s: features must be 16-byte aligned", who);
     if (a.keep_cell_map && h->p.nz != 1) return fail(PF_ERR_UNSUPPORTED, "%s: keep_cell_map needs nz == 1", who);
+    if (h->map_pending > 0)
+        return fail(PF_ERR_STATE, "%s: the cell map kept by the previous call (%d frames) was not consumed: call "
+                                  "pf_scatter_from_map or pf_discard_cell_map first", who, h->map_pending);
     DeviceGuard guard(h->device);
     cudaError_t e = pf::launch_voxelize(h->p, h->w, a, static_cast<cudaStream_t>(stream));
-    return e == cudaSuccess ? PF_OK : cuda_fail(e, who);
+    if (e != cudaSuccess) return cuda_fail(e, who);
+    h->map_pending = a.keep_cell_map ? a.n_frames : 0;
+    return PF_OK;
 }
 
 int pf_voxelize(pf_handle *h, const float *points, const int32_t *frame_offsets, int n_frames, int max_frame_points,
@@ -309,10 +315,26 @@ int pf_scatter_from_map(pf_handle *h, const float *feats, int64_t feat_stride_v,
     if (h->p.nz != 1) return fail(PF_ERR_UNSUPPORTED, "pf_scatter_from_map: needs nz == 1");
     if (n_frames < 1 || n_frames > h->max_frames) return fail(PF_ERR_CAPACITY, "pf_scatter_from_map: n_frames %d outside [1, %d]", n_frames, h->max_frames);
     if (n_ch < 1) return fail(PF_ERR_INVALID_ARGUMENT, "pf_scatter_from_map: n_ch < 1");
+    if (h->map_pending == 0) return fail(PF_ERR_STATE, "pf_scatter_from_map: no cell map is pending (voxelise with keep_cell_map first)");
+    if (n_frames != h->map_pending)
+        return fail(PF_ERR_INVALID_ARGUMENT, "pf_scatter_from_map: n_frames %d, but the kept map covers %d frames", n_frames, h->map_pending);
     DeviceGuard guard(h->device);
     cudaError_t e = pf::launch_scatter_from_map(h->p, h->w, feats, feat_stride_v, feat_stride_c, n_frames, compact, n_ch,
                                                 canvas, static_cast<cudaStream_t>(stream));
-    return e == cudaSuccess ? PF_OK : cuda_fail(e, "pf_scatter_from_map");
+    if (e != cudaSuccess) return cuda_fail(e, "pf_scatter_from_map");
+    h->map_pending = 0;   // the fill puts every cell it reads back to empty
+    return PF_OK;
+}
+
+int pf_discard_cell_map(pf_handle *h, void *stream)
+{
+    if (!h) return fail(PF_ERR_INVALID_ARGUMENT, "pf_discard_cell_map: null handle");
+    if (h->map_pending == 0) return PF_OK;
+    DeviceGuard guard(h->device);
+    cudaError_t e = pf::launch_fill_i32(h->w.grid, pf::kEmpty, (size_t)h->map_pending * h->p.cells, static_cast<cudaStream_t>(stream));
+    if (e != cudaSuccess) return cuda_fail(e, "pf_discard_cell_map");
+    h->map_pending = 0;
+    return PF_OK;
 }
 
 int pf_scatter_backward(const float *grad_canvas, const int32_t *coors, int coors_stride, int64_t n_voxels, int batch,

@@ -66,8 +66,9 @@ class PillarFrontEnd:
         self._g_inputs = None
 
     # ---- the two stages --------------------------------------------------------------------------
-    def voxelize_decorate(self, points, frame_offsets, n_frames=None, max_frame_points=None):
-        """points: CUDA fp32 (sum N_f, F); frame_offsets: CUDA int32 (n_frames+1,)."""
+    def voxelize_decorate(self, points, frame_offsets, n_frames=None, max_frame_points=None, keep_cell_map=True):
+        """points: CUDA fp32 (sum N_f, F); frame_offsets: CUDA int32 (n_frames+1,).  With ``keep_cell_map`` (default)
+        the call must be followed by exactly one ``scatter`` (or ``discard_cell_map``) before the next voxelise."""
         n_frames = self.B if n_frames is None else int(n_frames)
         mfp = self.max_points_per_frame if max_frame_points is None else int(max_frame_points)
         h = self.handle
@@ -75,10 +76,15 @@ class PillarFrontEnd:
         stream = torch.cuda.current_stream(self.device).cuda_stream
         _lib.check(h.lib.pf_voxelize_decorate(
             h.ptr, points.data_ptr(), frame_offsets.data_ptr(), n_frames, mfp, int(points.shape[1]),
-            1 if self.compact else 0, 4, vx, vy, xo, yo, 1,
+            1 if self.compact else 0, 4, vx, vy, xo, yo, 1 if keep_cell_map else 0,
             self.voxels.data_ptr() if self.voxels is not None else None, self.coors.data_ptr(),
             self.num_points.data_ptr(), self.voxel_num.data_ptr(), self.features.data_ptr(), stream),
             "pf_voxelize_decorate")
+
+    def discard_cell_map(self):
+        """Drop the cell map a voxelise call kept when no scatter follows it."""
+        h = self.handle
+        _lib.check(h.lib.pf_discard_cell_map(h.ptr, torch.cuda.current_stream(self.device).cuda_stream), "pf_discard_cell_map")
 
     def voxelize_pfn(self, points, frame_offsets, folded, n_frames=None, max_frame_points=None, want_features=False):
         """Fused voxelise + decorate + PFN (pf_voxelize_pfn): fills voxels/coors/num/voxel_num and ``self.pillar_feats``

@@ -361,7 +361,7 @@ def run_b200(args, rank, world, local):
         fmap = (int(geom.grid_size[0]) // 2, int(geom.grid_size[1]) // 2)         # feature_map_size of the configs
         am = amod.AnchorMask(synth.anchors_bv(geom, fmap), voxel_size=np.asarray(cfg["voxel_size"], np.float32),
                              offset=geom.offset, grid_size=geom.grid_size, device=local)
-        fe.voxelize_decorate(pts_d, offs_d)
+        fe.voxelize_decorate(pts_d, offs_d, keep_cell_map=False)      # no scatter follows: do not keep the cell map
         for _ in range(3):
             mask_d = fe.anchor_mask(am)
         torch.cuda.synchronize(dev)

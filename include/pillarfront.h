@@ -55,7 +55,8 @@ typedef enum pf_status {
     PF_ERR_INVALID_ARGUMENT = -1,
     PF_ERR_CAPACITY = -2,      /* n_frames / points per frame / voxels exceed what the handle was created for */
     PF_ERR_UNSUPPORTED = -3,   /* e.g. max_points > 255, num_features outside 3..16 */
-    PF_ERR_OUT_OF_MEMORY = -4
+    PF_ERR_OUT_OF_MEMORY = -4,
+    PF_ERR_STATE = -5          /* a kept cell map was not consumed (or none is pending): see pf_scatter_from_map */
 } pf_status;
 
 /* Grid geometry + caps: the attributes of the reference's VoxelGenerator (framework/voxel_generator.py:17-22). */
@@ -109,7 +110,10 @@ PF_API int pf_voxelize(pf_handle *h, const float *points, const int32_t *frame_o
 /* As pf_voxelize, and additionally writes the decorated pillar features; `voxels` may be NULL when only the
  * features are wanted.  vx, vy, x_off, y_off as PointNet.__init__ forms them (pointpillars8_shared.py:16-19).
  * keep_cell_map != 0 leaves the handle's cell->voxel map populated so that a following
- * pf_scatter_from_map can fill the canvas without re-indexing the coordinates (nz must be 1). */
+ * pf_scatter_from_map can fill the canvas without re-indexing the coordinates (nz must be 1).  The map must be
+ * consumed by exactly one pf_scatter_from_map over the same n_frames (or dropped with pf_discard_cell_map) before
+ * the handle voxelises again; otherwise the next voxelise call returns PF_ERR_STATE.  The bookkeeping is host-side
+ * and follows call order, so capture such a pair into a CUDA graph together, never one half of it. */
 PF_API int pf_voxelize_decorate(pf_handle *h, const float *points, const int32_t *frame_offsets, int n_frames,
                          int max_frame_points, int point_stride, int compact, int coors_stride,
                          float vx, float vy, float x_off, float y_off, int keep_cell_map,
@@ -155,6 +159,10 @@ PF_API int pf_scatter(pf_handle *h, const float *feats, int64_t feat_stride_v, i
  * frame f is row_base(f) + v with row_base = f*max_voxels (slab) or the running sum of voxel_num (compact). */
 PF_API int pf_scatter_from_map(pf_handle *h, const float *feats, int64_t feat_stride_v, int64_t feat_stride_c,
                         int n_frames, int compact, int n_ch, float *canvas, void *stream);
+
+/* Drop a kept cell map without filling a canvas (resets the grid cells of the pending frames); no-op when none is
+ * pending. */
+PF_API int pf_discard_cell_map(pf_handle *h, void *stream);
 
 /* grad_feats (v, c) = grad_canvas[b][c][x][y]; same stride convention as pf_scatter. */
 PF_API int pf_scatter_backward(const float *grad_canvas, const int32_t *coors, int coors_stride, int64_t n_voxels,

@@ -97,7 +97,7 @@ def test_batch_from_front_end_matches_oracle_per_frame(pf, gkey, fmap):
     pts = torch.from_numpy(np.concatenate(frames)).cuda()
     offs = torch.tensor(np.concatenate([[0], np.cumsum([len(f) for f in frames])]), dtype=torch.int32).cuda()
     fe = pf.PillarFrontEnd(cfg, max_batch=B, max_points_per_frame=n, want_voxels=False)
-    fe.voxelize_decorate(pts, offs)
+    fe.voxelize_decorate(pts, offs, keep_cell_map=False)
     bv = synth.anchors_bv(geom, fmap)
     a = _am(pf).AnchorMask(bv, voxel_size=np.asarray(cfg["voxel_size"], np.float32), offset=geom.offset,
                            grid_size=geom.grid_size)

@@ -205,7 +205,7 @@ def test_pipeline_with_fused_pfn(pf, gkey):
     with torch.no_grad():
         canvas = fe.step(pts, offs, pfn=net).clone()
         fused_rows = fe.pillar_feats.clone()
-        fe.voxelize_decorate(pts, offs)
+        fe.voxelize_decorate(pts, offs, keep_cell_map=False)
         want_rows = net.features_to_pillars(fe.features)
     counts = fe.voxel_num.cpu().numpy()
     for f in range(3):
@@ -251,3 +251,32 @@ def test_collate_of_device_outputs_equals_generate_batch(pf):
         assert torch.equal(merged[k], batch[k]), k
     conv = col.example_convert_to_torch(merged, device=merged["voxels"].device)
     assert conv["voxels"].data_ptr() == merged["voxels"].data_ptr()          # no copy for resident tensors
+
+
+def test_kept_cell_map_must_be_consumed(pf):
+    """A voxelise call that keeps its cell map must be followed by exactly one scatter (or a discard): the C ABI
+    refuses the next voxelise otherwise instead of silently producing empty frames."""
+    cfg = cfgmod.builtin_config("20cm")
+    cfg["max_voxels"] = 500
+    geom = cfgmod.derive_grid(cfg)
+    frames = [synth.make_frame("S1", geom, 4000, 61, 300), synth.make_frame("S3", geom, 3000, 62)]
+    pts = torch.from_numpy(np.concatenate(frames)).cuda()
+    offs = torch.tensor([0, 4000, 7000], dtype=torch.int32).cuda()
+    fe = pf.PillarFrontEnd(cfg, max_batch=2, max_points_per_frame=4000, device=0)
+    pillar = torch.randn((2 * 500, 64), device="cuda")
+    want = fe.step(pts, offs, pillar_feats=pillar).clone()
+    want_counts = fe.voxel_num.clone()
+    fe.voxelize_decorate(pts, offs)                                   # keeps the map ...
+    with pytest.raises(pf.PillarFrontError, match="not consumed"):
+        fe.voxelize_decorate(pts, offs)                               # ... so this is refused
+    with pytest.raises(pf.PillarFrontError, match="covers 2 frames"):
+        fe.scatter(pillar, n_frames=1)
+    fe.discard_cell_map()
+    with pytest.raises(pf.PillarFrontError, match="no cell map"):
+        fe.scatter(pillar)
+    fe.voxelize_decorate(pts, offs, keep_cell_map=False)              # nothing pending after this one
+    fe.voxelize_decorate(pts, offs, keep_cell_map=False)
+    assert torch.equal(fe.voxel_num, want_counts)
+    got = fe.step(pts, offs, pillar_feats=pillar)                     # and the handle still works, bit for bit
+    assert torch.equal(got, want) and torch.equal(fe.voxel_num, want_counts)
+    fe.close()

@@ -30,7 +30,7 @@ B = a.batch or (32 if "10cm" in a.grid else 8)
 frames, pts_cat, offs = bench.make_batch(pf, cfg, geom, B, 0)
 dev = torch.device("cuda", 0)
 fe = pf.PillarFrontEnd(cfg, max_batch=B, max_points_per_frame=cfg["frame_points"], device=0, want_voxels=False)
-fe.voxelize_decorate(torch.from_numpy(pts_cat).to(dev), torch.from_numpy(offs).to(dev))
+fe.voxelize_decorate(torch.from_numpy(pts_cat).to(dev), torch.from_numpy(offs).to(dev), keep_cell_map=False)
 fmap = (int(geom.grid_size[0]) // 2, int(geom.grid_size[1]) // 2)
 am = amod.AnchorMask(synth.anchors_bv(geom, fmap), voxel_size=np.asarray(cfg["voxel_size"], np.float32),
                      offset=geom.offset, grid_size=geom.grid_size)

@@ -19,15 +19,15 @@ def timed(offs_np, label, eager=False):
     offs_d = torch.from_numpy(offs_np).to(dev)
     s = torch.cuda.Stream(dev)
     with torch.cuda.stream(s):
-        for _ in range(3): fe.voxelize_decorate(pts, offs_d)
+        for _ in range(3): fe.voxelize_decorate(pts, offs_d, keep_cell_map=False)
     torch.cuda.synchronize()
     if not eager:
         g = torch.cuda.CUDAGraph()
         with torch.cuda.graph(g):
-            fe.voxelize_decorate(pts, offs_d)
+            fe.voxelize_decorate(pts, offs_d, keep_cell_map=False)
         run = g.replay
     else:
-        run = lambda: fe.voxelize_decorate(pts, offs_d)
+        run = lambda: fe.voxelize_decorate(pts, offs_d, keep_cell_map=False)
     for _ in range(5): run()
     torch.cuda.synchronize()
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)

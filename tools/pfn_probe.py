@@ -31,8 +31,8 @@ def timeit(fn, label, n=50):
 timeit(lambda: fe.step(pts, offs_d, pillar_feats=pillar), "no PFN (static pillar features; the bench step)")
 timeit(lambda: fe.step(pts, offs_d, pfn=net), "fused PFN (pf_voxelize_pfn + fill)")
 def unfused():
-    fe.voxelize_decorate(pts, offs_d)
+    fe.voxelize_decorate(pts, offs_d, keep_cell_map=False)
     fe.scatter(net.features_to_pillars(fe.features))
 timeit(unfused, "unfused PFN (decorate -> torch conv/bn/relu/max -> fill)")
 timeit(lambda: fe.voxelize_pfn(pts, offs_d, net.folded()), "  voxelize + decorate + PFN only (fused)")
-timeit(lambda: fe.voxelize_decorate(pts, offs_d), "  voxelize + decorate only")
+timeit(lambda: fe.voxelize_decorate(pts, offs_d, keep_cell_map=False), "  voxelize + decorate only")
