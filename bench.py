@@ -46,6 +46,7 @@ def parse_args():
     ap.add_argument("--no-single", action="store_true", help="skip the single-frame drop-in latency measurement")
     ap.add_argument("--no-pfn", action="store_true", help="skip the fused-vs-torch PFN side measurement")
     ap.add_argument("--no-anchor-mask", action="store_true", help="skip the anchor-mask (row N2) side measurement")
+    ap.add_argument("--e2e-eager", action="store_true", help="e2e arm: launch every copy / kernel eagerly instead of one graph per pipeline")
     ap.add_argument("--no-affinity", action="store_true",
                     help="do not pin the rank to the host cores NVML reports as local to its GPU (NUMA-local pinned buffers)")
     ap.add_argument("--device-pipelines", type=int, default=1,
@@ -422,19 +423,46 @@ def run_b200(args, rank, world, local):
     h2d = pts_cat.nbytes
     d2h = pipes[0]["h_cnt"].numel() * 4 + pipes[0]["h_coors"].numel() * 4
 
+    def e2e_body(p):
+        p["d_pts"].copy_(p["h_pts"], non_blocking=True)
+        p["fe"].step(p["d_pts"], offs_d, pillar_feats=pillar)
+        p["h_cnt"].copy_(p["fe"].voxel_num, non_blocking=True)
+        p["h_coors"].copy_(p["fe"].coors, non_blocking=True)
+
+    # each pipeline's whole step (H2D of the pinned points, the nine kernels, D2H of counts and coordinates) is one
+    # CUDA graph on the pipeline's stream, like the device arm; --e2e-eager launches it call by call instead
+    if not args.e2e_eager:
+        for p in pipes:
+            with torch.cuda.stream(p["stream"]):
+                for _ in range(2):
+                    e2e_body(p)
+            torch.cuda.synchronize(dev)
+            p["graph"] = torch.cuda.CUDAGraph()
+            with torch.cuda.graph(p["graph"], stream=p["stream"]):
+                e2e_body(p)
+        torch.cuda.synchronize(dev)
+
     def e2e_step(i):
         p = pipes[i % depth]
         with torch.cuda.stream(p["stream"]):
-            p["d_pts"].copy_(p["h_pts"], non_blocking=True)
-            p["fe"].step(p["d_pts"], offs_d, pillar_feats=pillar)
-            p["h_cnt"].copy_(p["fe"].voxel_num, non_blocking=True)
-            p["h_coors"].copy_(p["fe"].coors, non_blocking=True)
+            if args.e2e_eager:
+                e2e_body(p)
+            else:
+                p["graph"].replay()
 
     # the PCIe link and the pinned-copy path need far longer to reach steady state than the kernels do
     # (tools/e2e_probe.py: the first ~50 copies run at 20-27 GB/s, later ones at ~55 GB/s): untimed warm-up
-    w_e2e = max(W, 100)
-    for i in range(w_e2e):
-        e2e_step(i)
+    # ... and every pipeline has its own pinned buffer: warm up by step count AND by time (>= 100 steps per pipeline,
+    # >= 0.75 s), untimed
+    w_e2e = max(W, 100 * depth)
+    t_w0 = time.perf_counter()
+    n_w = 0
+    while n_w < w_e2e or time.perf_counter() - t_w0 < 0.75:
+        for _ in range(depth * 8):
+            e2e_step(n_w)
+            n_w += 1
+        torch.cuda.synchronize(dev)
+    w_e2e = n_w
     barrier()
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     e0.record(cur)
@@ -518,7 +546,8 @@ def main():
         "e2e": {"value": e2e_value, "unit": UNIT, "frames_per_s": r["tot_frames"] / r["t_e2e"],
                 "ms_per_step": 1e3 * r["t_e2e"] / K, "h2d_bytes_per_step": r["h2d"], "d2h_bytes_per_step": r["d2h"],
                 "api": "PillarFrontEnd.step on pinned host points; D2H of voxel_num + coordinates; canvas stays "
-                       "on the GPU for the backbone, as in the reference", "pipelines": r["depth"], "warmup_steps": r["w_e2e"]},
+                       "on the GPU for the backbone, as in the reference", "pipelines": r["depth"], "warmup_steps": r["w_e2e"],
+                "launch": "eager" if args.e2e_eager else "one CUDA graph per pipeline (H2D + kernels + D2H)"},
         "gpu_launches": K * (fe.n_kernels_voxelize(cfg["frame_points"]) + fe.N_KERNELS_SCATTER),
         "clocks": r["clocks"],
         "stages_ms": {"voxelize_decorate": 1e3 * r["t_vox"], "scatter": 1e3 * r["t_scat"]},
