@@ -38,41 +38,42 @@ def _pad_frame_id(coor, i):
     return np.pad(coor, ((0, 0), (0, 1)), mode="constant", constant_values=i)
 
 
+_CONCAT_KEYS = frozenset({"voxels", "num_points_per_voxel", "match_indices_num"})   # joined along axis 0
+_INT32_KEYS = frozenset({"coordinates", "num_points_per_voxel", "voxel_num"})
+
+
+def _stack(elems):
+    if any(_is_tensor(e) for e in elems):
+        import torch
+        dev = next(e.device for e in elems if _is_tensor(e))
+        return torch.stack([e if _is_tensor(e) else torch.as_tensor(e, device=dev) for e in elems], dim=0)
+    return np.stack(elems, axis=0)
+
+
 def merge_second_batch(batch_list, _unused=False):
-    example_merged = defaultdict(list)
+    """Collate per-frame example dicts (framework/utils.py:23-48): see the module docstring for the layout."""
+    columns = defaultdict(list)
     for example in batch_list:
-        for k, v in example.items():
-            example_merged[k].append(v)
-    ret = {}
-    for key, elems in example_merged.items():
-        if key in ("voxels", "num_points_per_voxel", "match_indices_num"):
-            ret[key] = _cat(elems)
-        elif key == "coordinates":
-            if len(batch_list) > 1:
-                ret[key] = _cat([_pad_frame_id(c, i) for i, c in enumerate(elems)])
-            else:
-                ret[key] = _cat(elems)
-        elif any(_is_tensor(e) for e in elems):
-            import torch
-            dev = next(e.device for e in elems if _is_tensor(e))
-            ret[key] = torch.stack([e if _is_tensor(e) else torch.as_tensor(e, device=dev) for e in elems], dim=0)
+        for key, value in example.items():
+            columns[key].append(value)
+    pad_frame = len(batch_list) > 1            # the reference pads the frame id only for a real batch
+    merged = {}
+    for key, elems in columns.items():
+        if key == "coordinates":
+            merged[key] = _cat([_pad_frame_id(c, i) for i, c in enumerate(elems)] if pad_frame else elems)
+        elif key in _CONCAT_KEYS:
+            merged[key] = _cat(elems)
         else:
-            ret[key] = np.stack(elems, axis=0)
-    return ret
+            merged[key] = _stack(elems)
+    return merged
 
 
 def example_convert_to_torch(example, dtype=None, device=None):
+    """Move the tensors of an example to ``device`` (framework/utils.py:7-20): ``voxels`` in ``dtype`` (float32),
+    coordinates / counts as int32, ``anchors_mask`` as bool, everything else untouched.  Tensors already there with
+    the right dtype are returned as they are (no copy)."""
     import torch
-    dtype = torch.float32 if dtype is None else dtype
     device = torch.device("cuda:0") if device is None else torch.device(device)
-    example_torch = {}
-    for k, v in example.items():
-        if k in ("voxels",):
-            example_torch[k] = torch.as_tensor(v, dtype=dtype, device=device)
-        elif k in ("coordinates", "num_points_per_voxel", "voxel_num"):
-            example_torch[k] = torch.as_tensor(v, dtype=torch.int32, device=device)
-        elif k in ("anchors_mask",):
-            example_torch[k] = torch.as_tensor(v, dtype=torch.bool, device=device)
-        else:
-            example_torch[k] = v
-    return example_torch
+    casts = {"voxels": torch.float32 if dtype is None else dtype, "anchors_mask": torch.bool}
+    casts.update({k: torch.int32 for k in _INT32_KEYS})
+    return {k: (torch.as_tensor(v, dtype=casts[k], device=device) if k in casts else v) for k, v in example.items()}
