@@ -429,7 +429,7 @@ def run_b200(args, rank, world, local):
         p["h_cnt"].copy_(p["fe"].voxel_num, non_blocking=True)
         p["h_coors"].copy_(p["fe"].coors, non_blocking=True)
 
-    # each pipeline's whole step (H2D of the pinned points, the nine kernels, D2H of counts and coordinates) is one
+    # each pipeline's whole step (H2D of the pinned points, the eight kernels, D2H of counts and coordinates) is one
     # CUDA graph on the pipeline's stream, like the device arm; --e2e-eager launches it call by call instead
     if not args.e2e_eager:
         for p in pipes:

@@ -14,7 +14,7 @@ timeout 600 python bench.py --impl reference --steps 5 --warmup 1 > $o/${tag}_be
 timeout 300 python bench.py --steps 30 --warmup 5 --no-cpu-baseline --no-pfn --no-single > $o/${tag}_ll_plain.json 2> /dev/null && \
 timeout 900 ncu --metrics gpu__time_duration.sum --clock-control none -c 400 --csv --log-file $o/${tag}_launches.csv \
     python bench.py --steps 30 --warmup 5 --no-cpu-baseline --no-pfn --no-single > $o/${tag}_ll_ncu.log 2>&1
-# full-set capture of one eager step (9 kernels at these frame sizes), after two warm-up steps
+# full-set capture of one eager step (8 launches at these frame sizes; the 9-launch window also shows the next step's first), after warm-up steps
 for g in 20cm nuscene; do
   timeout 120 python tools/prof_step.py --grid $g --steps 4 > $o/${tag}_plain_$g.log 2>&1 && \
   timeout 900 ncu --set full --clock-control none --import-source on -k regex:^k_ -s 20 -c 9 -f -o $o/${tag}_step_$g \
