@@ -16,6 +16,7 @@ _LAZY = {
     "AnchorMask": "anchor_mask", "get_anchor_coor": "anchor_mask", "fused_get_anchors_mask_gpu": "anchor_mask",
     "merge_second_batch": "collate", "example_convert_to_torch": "collate",
     "nms_gpu": "nms", "nms": "nms", "nms_device": "nms",
+    "Inference": "inference", "PostProcessor": "inference",
     "PillarFrontEnd": "frontend", "shard_frames": "sharding", "PillarFrontError": "_lib",
 }
 

@@ -12,13 +12,31 @@ LIB_PATH = Path(__file__).resolve().parent / "lib" / "libpillarfront.so"
 EXPORTS = ["pf_version", "pf_last_error_string", "pf_create", "pf_destroy", "pf_workspace_bytes",
            "pf_voxelize", "pf_voxelize_decorate", "pf_voxelize_pfn", "pf_pfn", "pf_decorate", "pf_scatter", "pf_scatter_from_map",
            "pf_scatter_backward", "pf_anchor_mask", "pf_nms", "pf_nms_scratch_bytes",
-           "pf_debug_stage_timing", "pf_debug_stage_times", "pf_discard_cell_map"]
+           "pf_debug_stage_timing", "pf_debug_stage_times", "pf_discard_cell_map",
+           "pf_postprocess", "pf_post_scratch_bytes", "pf_post_scratch_layout"]
 
 
 class GridDesc(C.Structure):
     """pf_grid_desc"""
     _fields_ = [("offset", C.c_float * 3), ("voxel_size", C.c_float * 3), ("grid", C.c_int32 * 3),
                 ("max_voxels", C.c_int32), ("max_points", C.c_int32), ("num_features", C.c_int32)]
+
+
+class PostDesc(C.Structure):
+    """pf_post_desc"""
+    _fields_ = [("n_classes", C.c_int32), ("class_range", (C.c_int32 * 2) * 8), ("n_cls_channels", C.c_int32),
+                ("pre_max", C.c_int32), ("post_max", C.c_int32), ("score_threshold", C.c_float),
+                ("iou_threshold", C.c_float), ("center_limit", C.c_double * 6)]
+
+
+# pf_post_region: name -> (index, torch dtype of the region, columns per row)
+POST_REGION_NAMES = ["cand", "cand_count", "sel_key", "sel_num", "seg_offsets", "sel_anchor", "sel_score", "sel_box",
+                     "sel_standup", "sel_dir", "sel_rank", "keep", "keep_num", "nms_scratch"]
+_POST_TYPES = {"cand": ("int64", 1), "cand_count": ("int32", 1), "sel_key": ("int64", 1), "sel_num": ("int32", 1),
+               "seg_offsets": ("int32", 1), "sel_anchor": ("int32", 1), "sel_score": ("float32", 1),
+               "sel_box": ("float32", 7), "sel_standup": ("float32", 4), "sel_dir": ("int32", 1),
+               "sel_rank": ("float32", 1), "keep": ("int32", 1), "keep_num": ("int32", 1), "nms_scratch": ("uint8", 1)}
+POST_REGIONS = {n: (i, *_POST_TYPES[n]) for i, n in enumerate(POST_REGION_NAMES)}
 
 
 class PillarFrontError(RuntimeError):
@@ -84,6 +102,12 @@ def load():
     L.pf_nms_scratch_bytes.argtypes = [C.c_int, C.c_int]
     L.pf_nms.restype = C.c_int
     L.pf_nms.argtypes = [_p, _p, _p, C.c_int, C.c_int64, C.c_int, C.c_float, C.c_int, _p, _p, _p, _p]
+    L.pf_post_scratch_bytes.restype = C.c_size_t
+    L.pf_post_scratch_bytes.argtypes = [C.POINTER(PostDesc), C.c_int, C.c_int64]
+    L.pf_post_scratch_layout.restype = C.c_size_t
+    L.pf_post_scratch_layout.argtypes = [C.POINTER(PostDesc), C.c_int, C.c_int64, C.POINTER(C.c_size_t)]
+    L.pf_postprocess.restype = C.c_int
+    L.pf_postprocess.argtypes = [C.POINTER(PostDesc), _p, _p, _p, _p, _p, C.c_int, C.c_int64, _p, _p, _p, _p, _p, _p, _p]
     _lib = L
     return L
 
@@ -92,6 +116,20 @@ def check(rc: int, what: str = "") -> None:
     if rc != 0:
         msg = load().pf_last_error_string().decode("utf-8", "replace")
         raise PillarFrontError(f"{what or 'libpillarfront'} failed (status {rc}): {msg}")
+
+
+def make_post_desc(class_ranges, n_cls_channels, pre_max, post_max, score_threshold, iou_threshold, center_limit) -> PostDesc:
+    if not 1 <= len(class_ranges) <= 8:
+        raise ValueError(f"{len(class_ranges)} classes: pf_postprocess handles 1..8")
+    d = PostDesc()
+    d.n_classes = len(class_ranges)
+    for c, (lo, hi) in enumerate(class_ranges):
+        d.class_range[c][0], d.class_range[c][1] = int(lo), int(hi)
+    d.n_cls_channels, d.pre_max, d.post_max = int(n_cls_channels), int(pre_max), int(post_max)
+    d.score_threshold, d.iou_threshold = float(score_threshold), float(iou_threshold)
+    for i in range(6):
+        d.center_limit[i] = float(center_limit[i])
+    return d
 
 
 def make_desc(geom, max_voxels: int, max_points: int, num_features: int) -> GridDesc:

@@ -17,7 +17,7 @@ ROOT = PKG.parent
 CSRC = PKG / "csrc"
 LIB_DIR = PKG / "lib"
 LIB = LIB_DIR / "libpillarfront.so"
-SOURCES = ["pf_api.cu", "pf_voxelize.cu", "pf_gather.cu", "pf_scatter.cu", "pf_anchor.cu", "pf_nms.cu"]
+SOURCES = ["pf_api.cu", "pf_voxelize.cu", "pf_gather.cu", "pf_scatter.cu", "pf_anchor.cu", "pf_nms.cu", "pf_post.cu"]
 NVCC_FLAGS = ["-gencode", "arch=compute_100a,code=sm_100a", "-O3", "-lineinfo", "-std=c++17",
               "--shared", "-Xcompiler", "-fPIC,-Wall,-Wextra,-fvisibility=hidden",
               "-Xptxas", "-v", "--fmad=false"]
@@ -34,7 +34,7 @@ def needs_build() -> bool:
     if not LIB.exists():
         return True
     t = LIB.stat().st_mtime
-    deps = list(CSRC.glob("*.cu")) + list(CSRC.glob("*.cuh")) + [ROOT / "include" / "pillarfront.h", Path(__file__)]
+    deps = list(CSRC.glob("*.cu")) + list(CSRC.glob("*.cuh")) + list(CSRC.glob("*.h")) + [ROOT / "include" / "pillarfront.h", Path(__file__)]
     return any(d.stat().st_mtime > t for d in deps)
 
 

@@ -396,3 +396,67 @@ int pf_nms(const float *boxes, const float *scores, const int32_t *seg_offsets, 
 }
 
 }  // extern "C"
+
+namespace {
+
+// validates a pf_post_desc and the batch shape; 0 = fine
+int post_check(const pf_post_desc *d, int n_frames, int64_t n_anchors, const char *who)
+{
+    if (!d) return fail(PF_ERR_INVALID_ARGUMENT, "%s: null desc", who);
+    if (d->n_classes < 1 || d->n_classes > pf::post::kMaxClasses) return fail(PF_ERR_UNSUPPORTED, "%s: n_classes %d outside 1..%d", who, d->n_classes, pf::post::kMaxClasses);
+    if (d->n_cls_channels < 1) return fail(PF_ERR_INVALID_ARGUMENT, "%s: n_cls_channels < 1", who);
+    if (d->pre_max < 1 || d->pre_max > 4096) return fail(PF_ERR_UNSUPPORTED, "%s: pre_max %d outside 1..4096", who, d->pre_max);
+    if (d->post_max < 1 || d->post_max > pf::post::kFinishThreads) return fail(PF_ERR_UNSUPPORTED, "%s: post_max %d outside 1..%d", who, d->post_max, pf::post::kFinishThreads);
+    if (n_frames < 1 || n_frames > 65535) return fail(PF_ERR_INVALID_ARGUMENT, "%s: n_frames %d outside 1..65535", who, n_frames);
+    if (n_anchors < 0 || n_anchors >= (1ll << 31)) return fail(PF_ERR_INVALID_ARGUMENT, "%s: n_anchors out of range", who);
+    if ((long long)n_frames * d->n_classes > 65535) return fail(PF_ERR_CAPACITY, "%s: %lld segments > 65535", who, (long long)n_frames * d->n_classes);
+    for (int c = 0; c < d->n_classes; ++c) {
+        const long long lo = d->class_range[c][0], hi = d->class_range[c][1];
+        if (lo < 0 || hi < lo || hi > n_anchors) return fail(PF_ERR_INVALID_ARGUMENT, "%s: class_range[%d] = [%lld, %lld) outside [0, %lld]", who, c, lo, hi, (long long)n_anchors);
+        for (int e = 0; e < c; ++e)
+            if (lo < d->class_range[e][1] && d->class_range[e][0] < hi) return fail(PF_ERR_INVALID_ARGUMENT, "%s: class ranges %d and %d overlap", who, e, c);
+    }
+    return 0;
+}
+
+}  // namespace
+
+extern "C" {
+
+size_t pf_post_scratch_layout(const pf_post_desc *d, int n_frames, int64_t n_anchors, size_t *offsets)
+{
+    if (post_check(d, n_frames, n_anchors, "pf_post_scratch_layout") != 0) return 0;
+    return pf::post_scratch_layout(d->n_classes, d->pre_max, d->post_max, n_frames, n_anchors, offsets);
+}
+
+size_t pf_post_scratch_bytes(const pf_post_desc *d, int n_frames, int64_t n_anchors)
+{
+    return pf_post_scratch_layout(d, n_frames, n_anchors, nullptr);
+}
+
+int pf_postprocess(const pf_post_desc *d, const float *cls_preds, const float *box_preds, const float *dir_preds,
+                   const uint8_t *anchors_mask, const float *anchors, int n_frames, int64_t n_anchors, void *scratch,
+                   float *det_boxes, float *det_scores, int32_t *det_class, int32_t *det_anchor, int32_t *det_num,
+                   void *stream)
+{
+    if (n_frames == 0) return PF_OK;
+    const int rc = post_check(d, n_frames, n_anchors, "pf_postprocess");
+    if (rc != 0) return rc;
+    if (!scratch || (reinterpret_cast<uintptr_t>(scratch) & 255)) return fail(PF_ERR_INVALID_ARGUMENT, "pf_postprocess: scratch must be non-null and 256-byte aligned");
+    if (!det_boxes || !det_scores || !det_class || !det_num) return fail(PF_ERR_INVALID_ARGUMENT, "pf_postprocess: null output");
+    if (n_anchors > 0 && (!cls_preds || !box_preds || !dir_preds || !anchors)) return fail(PF_ERR_INVALID_ARGUMENT, "pf_postprocess: null input");
+    pf::post::Desc k{};
+    k.n_classes = d->n_classes;
+    for (int c = 0; c < d->n_classes; ++c) k.lo[c] = d->class_range[c][0], k.hi[c] = d->class_range[c][1];
+    k.n_ch = d->n_cls_channels;
+    k.pre_max = d->pre_max;
+    k.post_max = d->post_max;
+    k.score_thr = d->score_threshold;
+    for (int i = 0; i < 6; ++i) k.limit[i] = d->center_limit[i];
+    cudaError_t e = pf::launch_postprocess(k, d->iou_threshold, cls_preds, box_preds, dir_preds, anchors_mask, anchors, n_frames,
+                                           n_anchors, scratch, det_boxes, det_scores, det_class, det_anchor, det_num,
+                                           static_cast<cudaStream_t>(stream));
+    return e == cudaSuccess ? PF_OK : cuda_fail(e, "pf_postprocess");
+}
+
+}  // extern "C"

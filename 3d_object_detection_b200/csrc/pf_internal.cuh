@@ -5,6 +5,7 @@
 #include <stdint.h>
 
 #include "pillarfront.h"
+#include "pf_post_desc.h"
 
 namespace pf {
 
@@ -121,6 +122,12 @@ size_t nms_scratch_bytes(int n_seg, int max_seg);
 cudaError_t launch_nms(const float *boxes, const float *scores, const int32_t *seg_offsets, int n_seg, long long n_total,
                        int max_seg, float thresh, int post_max, void *scratch, int32_t *keep, int32_t *keep_num,
                        cudaStream_t stream);
+
+size_t post_scratch_layout(int n_classes, int pre_max, int post_max, int n_frames, long long n_anchors, size_t *offsets);
+cudaError_t launch_postprocess(const post::Desc &d, float iou_threshold, const float *cls_preds, const float *box_preds,
+                               const float *dir_preds, const uint8_t *anchors_mask, const float *anchors, int n_frames,
+                               long long n_anchors, void *scratch, float *det_boxes, float *det_scores, int32_t *det_class,
+                               int32_t *det_anchor, int32_t *det_num, cudaStream_t stream);
 
 // ---- small device helpers -------------------------------------------------------------------------------
 #ifdef __CUDACC__

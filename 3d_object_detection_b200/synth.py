@@ -165,3 +165,46 @@ def nms_dets(n: int, seed: int) -> np.ndarray:
     boxes = np.concatenate([c - wh / 2, c + wh / 2], 1)
     scores = rng.permutation(n).astype(np.float64) / n * 0.9 + 0.05 + rng.uniform(0, 1e-3, n)   # distinct scores
     return np.concatenate([boxes, scores[:, None]], 1).astype(np.float32)
+
+
+def anchors_3d(geom: GridGeometry, feature_map=(400, 400), classes=ANCHOR_CLASSES):
+    """Synthetic 7-number anchors (A, 7) fp32 = (x, y, z, l, w, h, yaw), one per feature-map cell, size and yaw, laid
+    out like AnchorAssigner builds them (framework/anchor_assigner.py:252-289, generate :301-320): all cells of one
+    (size, yaw) pair contiguously, x slow.  Also returns the class ranges [[start, end), ...] (class_masks) of the
+    reference's three classes: the first three sizes are "vehicle", then "pedestrian", then "cyclist"."""
+    fx, fy = int(feature_map[0]), int(feature_map[1])
+    diff = np.asarray(geom.range_diff, np.float32)
+    off = np.asarray(geom.offset, np.float32)
+    sx, sy = diff[0] / np.float32(fx), diff[1] / np.float32(fy)
+    cx = np.arange(fx, dtype=np.float32) * sx + (off[0] + sx / 2)
+    cy = np.arange(fy, dtype=np.float32) * sy + (off[1] + sy / 2)
+    gx, gy = np.meshgrid(cx, cy, indexing="ij")
+    gx, gy = gx.reshape(-1), gy.reshape(-1)
+    out, per_size = [], []
+    for (l, w, h), yaws in classes:
+        n0 = sum(len(o) for o in out)
+        for yaw in yaws:
+            a = np.empty((gx.size, 7), np.float32)
+            a[:, 0], a[:, 1], a[:, 2] = gx, gy, np.float32(h / 2)
+            a[:, 3], a[:, 4], a[:, 5], a[:, 6] = l, w, h, yaw
+            out.append(a)
+        per_size.append((n0, sum(len(o) for o in out)))
+    anchors = np.ascontiguousarray(np.concatenate(out, axis=0))
+    if len(per_size) == 5:          # the reference's set: three vehicle sizes, pedestrian, cyclist
+        ranges = [[per_size[0][0], per_size[2][1]], list(per_size[3]), list(per_size[4])]
+    else:
+        ranges = [list(r) for r in per_size]
+    return anchors, ranges
+
+
+def post_preds(n_frames: int, n_anchors: int, seed: int, mean_logit: float = -6.0, mask_frac: float = 0.7):
+    """Synthetic network-head outputs for the post-processing row: class logits (B, A, 1) ~ N(mean_logit, 2) (about 6 %
+    above the 0.05 score threshold at -6), box encodings (B, A, 7) ~ N(0, 0.25) with yaw residuals U(-pi, pi), direction
+    logits (B, A, 2), and an anchor mask (B, A) bool."""
+    rng = np.random.default_rng(seed)
+    cls = rng.normal(mean_logit, 2.0, (n_frames, n_anchors, 1)).astype(np.float32)
+    box = rng.normal(0.0, 0.25, (n_frames, n_anchors, 7)).astype(np.float32)
+    box[..., 6] = rng.uniform(-np.pi, np.pi, (n_frames, n_anchors)).astype(np.float32)
+    dirp = rng.normal(0.0, 1.0, (n_frames, n_anchors, 2)).astype(np.float32)
+    mask = rng.random((n_frames, n_anchors)) < mask_frac
+    return cls, box, dirp, mask

@@ -22,6 +22,9 @@
  *   pf_nms               <-> framework/nms.py:6-44 (nms_gpu: host argsort, nms_kernel :116-147 with iou_device
  *                            :102-113, host nms_postprocess :85-99), called through nms(), framework/inference.py:689-703
  *                            ("next" row N4)
+ *   pf_postprocess       <-> framework/inference.py:26-138 (Inference.infer_gpu: anchor mask, sigmoid, score mask,
+ *                            top-k, box_np_ops.box_decode :406-424, standup boxes, nms, direction flip, range mask,
+ *                            limit_period), batched over frames and classes (row N4, the part around pf_nms)
  *
  * Conventions
  *   - plain pointers and sizes only; every pointer named *device* is CUDA device memory on the handle's
@@ -205,6 +208,70 @@ PF_API size_t pf_nms_scratch_bytes(int n_segments, int max_segment_boxes);
 PF_API int pf_nms(const float *boxes, const float *scores, const int32_t *seg_offsets, int n_segments, int64_t n_total,
            int max_segment_boxes, float iou_threshold, int post_max, void *scratch, int32_t *keep,
            int32_t *keep_num, void *stream);
+
+/* Detection post-processing of a batch of frames, entirely on the device: the per-class loop of
+ * Inference.infer_gpu (framework/inference.py:26-138) around pf_nms --
+ *   anchor mask (:44-47), sigmoid + max over the class channels (:50-54), score mask (:58-64), top-k (:67-69),
+ *   box_decode (framework/box_np_ops.py:406-424), centre boxes -> corners -> standup boxes (box_np_ops.py:81-99,
+ *   122-153, 64-78, 899-904), nms (:85-91), direction flip (:97-104), range mask (:106-109), limit_period (:113).
+ * The reference does this per frame and class with ~10 device synchronisations, a device->host copy of the top-k
+ * rows, numpy decoding, and the numba NMS; here one call handles n_frames * n_classes segments in seven launches.
+ *
+ *   cls_preds    device float [n_frames][n_anchors][n_cls_channels]   (logits)
+ *   box_preds    device float [n_frames][n_anchors][7]                (x, y, z, l, w, h, r encodings)
+ *   dir_preds    device float [n_frames][n_anchors][2]
+ *   anchors_mask device uint8 [n_frames][n_anchors] (numpy bool layout, e.g. the output of pf_anchor_mask), or NULL
+ *   anchors      device float [n_anchors][7]
+ *   scratch      device, pf_post_scratch_bytes(...) bytes, 256-byte aligned
+ *   det_boxes    device float [n_frames][n_classes * post_max][7]   location (3), dimensions (3), rotation_y
+ *   det_scores   device float [n_frames][n_classes * post_max]
+ *   det_class    device int32 [n_frames][n_classes * post_max]      index into class_range (detect_class order)
+ *   det_anchor   device int32 [n_frames][n_classes * post_max] or NULL: the anchor each detection came from
+ *   det_num      device int32 [n_frames]: valid rows of each frame; they are ordered like the reference's
+ *                concatenated lists (classes in class_range order, descending score inside a class)
+ *
+ * Order: the reference sorts by the sigmoid score and leaves ties undefined (torch.topk, numpy argsort); this
+ * library orders by (logit descending, anchor index ascending), which refines that order and does not depend on an
+ * exp() implementation.  x, y, rotation_y are bit-exact restatements of the numpy arithmetic; z and the dimensions
+ * go through expf and are a few ulp from numpy's.  NaN logits never pass the score mask (as in the reference). */
+typedef struct pf_post_desc {
+    int32_t n_classes;          /* 1..8 */
+    int32_t class_range[8][2];  /* [start, end) anchor indices of each class: AnchorAssigner.class_masks */
+    int32_t n_cls_channels;     /* last dimension of cls_preds (1 in the reference's head) */
+    int32_t pre_max;            /* Inference._nms_pre_max_size (1000), 1..4096 */
+    int32_t post_max;           /* Inference._nms_post_max_size (300), 1..1024 */
+    float score_threshold;      /* Inference._nms_score_threshold (0.05) */
+    float iou_threshold;        /* Inference._nms_iou_threshold (0.1) */
+    double center_limit[6];     /* config['center_limit'] */
+} pf_post_desc;
+
+/* Regions of the scratch buffer (byte offsets from pf_post_scratch_layout): intermediate results a caller or a
+ * test may read after the call.  "rows" are indexed seg_offsets[segment] + rank, segment = frame * n_classes + class. */
+typedef enum pf_post_region {
+    PF_POST_CAND = 0,        /* uint64 candidate keys                                  */
+    PF_POST_CAND_COUNT,      /* int32 [segments] anchors that passed mask and threshold */
+    PF_POST_SEL_KEY,         /* uint64 [segments][pre_max] selected keys, best first     */
+    PF_POST_SEL_NUM,         /* int32 [segments] min(candidates, pre_max)                */
+    PF_POST_SEG_OFFSETS,     /* int32 [segments + 1] running sum of SEL_NUM              */
+    PF_POST_SEL_ANCHOR,      /* int32 rows: anchor index                                 */
+    PF_POST_SEL_SCORE,       /* float rows: sigmoid score                                */
+    PF_POST_SEL_BOX,         /* float rows x 7: decoded boxes                            */
+    PF_POST_SEL_STANDUP,     /* float rows x 4: standup boxes handed to the NMS          */
+    PF_POST_SEL_DIR,         /* int32 rows: direction label                              */
+    PF_POST_SEL_RANK,        /* float rows: pre_max - rank (the NMS sort key)            */
+    PF_POST_KEEP,            /* int32 [segments][post_max] kept ranks, -1 padded         */
+    PF_POST_KEEP_NUM,        /* int32 [segments]                                         */
+    PF_POST_NMS_SCRATCH,
+    PF_POST_REGIONS
+} pf_post_region;
+
+PF_API size_t pf_post_scratch_bytes(const pf_post_desc *desc, int n_frames, int64_t n_anchors);
+/* offsets: size_t [PF_POST_REGIONS]; returns the total (0 on invalid arguments). */
+PF_API size_t pf_post_scratch_layout(const pf_post_desc *desc, int n_frames, int64_t n_anchors, size_t *offsets);
+PF_API int pf_postprocess(const pf_post_desc *desc, const float *cls_preds, const float *box_preds, const float *dir_preds,
+                   const uint8_t *anchors_mask, const float *anchors, int n_frames, int64_t n_anchors, void *scratch,
+                   float *det_boxes, float *det_scores, int32_t *det_class, int32_t *det_anchor, int32_t *det_num,
+                   void *stream);
 
 #ifdef __cplusplus
 }

@@ -278,3 +278,133 @@ def nms(bboxes, scores, pre_max_size=None, post_max_size=None, iou_threshold=0.5
     else:
         keep = np.array(nms_gpu(dets, iou_threshold), dtype=np.int64)[:post_max_size]
     return None if keep.shape[0] == 0 else keep
+
+
+# ---- detection post-processing (row N4 around the NMS): Inference.infer_gpu, framework/inference.py:26-138 -----------
+
+def sigmoid32(x):
+    """torch.sigmoid in fp32, written as 1 / (1 + exp(-x)) (framework/inference.py:50)."""
+    x = np.asarray(x, np.float32)
+    with np.errstate(over="ignore"):
+        return (np.float32(1.0) / (np.float32(1.0) + np.exp(-x))).astype(np.float32)
+
+
+def box_decode(box_encodings, anchors):
+    """box_decode, framework/box_np_ops.py:406-424 (the live definition; the one at :386 is inside a string)."""
+    xa, ya, za, la, wa, ha, ra = np.split(anchors, 7, axis=-1)
+    xt, yt, zt, lt, wt, ht, rt = np.split(box_encodings, 7, axis=-1)
+    za = za + ha / 2
+    diagonal = np.sqrt(la ** 2 + wa ** 2)
+    xg = xt * diagonal + xa
+    yg = yt * diagonal + ya
+    zg = zt * ha + za
+    lg = np.exp(lt) * la
+    wg = np.exp(wt) * wa
+    hg = np.exp(ht) * ha
+    rg = rt + ra
+    zg = zg - hg / 2
+    return np.concatenate([xg, yg, zg, lg, wg, hg, rg], axis=-1)
+
+
+def standup_boxes(boxes_for_nms):
+    """center_to_corner_box2d (framework/box_np_ops.py:81-99: corners_nd :122-153 with origin 0.5, rotation_2d :64-78,
+    + centres) followed by corner_to_standup_nd (:899-904), on rows (x, y, l, w, r)."""
+    b = np.asarray(boxes_for_nms)
+    centers, dims, angles = b[:, :2], b[:, 2:4], b[:, 4]
+    corners_norm = np.array([[0, 0], [0, 1], [1, 1], [1, 0]], dtype=dims.dtype) - np.array(0.5, dtype=dims.dtype)
+    corners = dims.reshape([-1, 1, 2]) * corners_norm.reshape([1, 4, 2])
+    rot_sin, rot_cos = np.sin(angles), np.cos(angles)
+    rot_mat_T = np.stack([[rot_cos, rot_sin], [-rot_sin, rot_cos]])
+    corners = np.einsum('aij,jka->aik', corners, rot_mat_T)
+    corners += centers.reshape([-1, 1, 2])
+    return np.concatenate([np.min(corners, axis=1), np.max(corners, axis=1)], -1)
+
+
+def limit_period(val, offset=0.5, period=np.pi):
+    """framework/box_np_ops.py:102-103."""
+    return val - np.floor(val / period + offset) * period
+
+
+def post_select(cls_logits, a_mask, score_threshold, pre_max):
+    """framework/inference.py:44-69 for one class range of one frame: anchor mask, sigmoid, max over the class channels,
+    score mask, top-k.  Returns the local anchor indices of the selected boxes, best first, and their scores.
+    The reference orders by score and leaves ties open; the order stated here is (max logit descending, anchor index
+    ascending), a refinement of it that needs no exp()."""
+    logits = np.asarray(cls_logits, np.float32).reshape(len(cls_logits), -1)
+    with np.errstate(invalid="ignore"):
+        top_logit = logits.max(axis=1)                 # NaN propagates, and a NaN score fails the threshold test
+    score = sigmoid32(top_logit)
+    ok = score >= np.float32(score_threshold)
+    if a_mask is not None:
+        ok &= np.asarray(a_mask, bool)
+    idx = np.nonzero(ok)[0]
+    # total order on the logits: the usual monotone float -> uint32 map (so -0.0 sorts just below +0.0)
+    u = np.ascontiguousarray(top_logit[idx]).view(np.uint32).astype(np.int64)
+    key = np.where(u & 0x80000000, ~u & 0xFFFFFFFF, u | 0x80000000)
+    order = np.argsort(-key, kind="stable")
+    sel = idx[order][:pre_max]
+    return sel.astype(np.int64), score[sel]
+
+
+def post_finish(boxes, top_scores, dir_labels, selected, center_limit):
+    """framework/inference.py:97-114 for one class: NMS mask, direction flip, range mask, limit_period.  Returns the
+    surviving boxes and scores and the range mask over `selected`."""
+    boxes = np.array(boxes, np.float32)[selected]
+    scores = np.asarray(top_scores)[selected]
+    dir_mask = boxes[..., -1] > 0
+    opp = dir_mask ^ np.asarray(dir_labels).astype(bool)[selected]
+    boxes[..., -1] += np.where(opp, np.pi, 0.0)
+    limit = list(center_limit)
+    min_mask = np.any(boxes[:, :3] > limit[:3], axis=1)
+    max_mask = np.any(boxes[:, 3:6] < limit[3:], axis=1)
+    range_mask = min_mask & max_mask
+    boxes = boxes[range_mask]
+    boxes[..., -1] = limit_period(boxes[..., -1], period=2 * np.pi)
+    return boxes, scores[range_mask], range_mask
+
+
+def postprocess_frame(cls_preds, box_preds, dir_preds, anchors_mask, anchors, class_ranges, center_limit,
+                      score_threshold=0.05, pre_max=1000, post_max=300, iou_threshold=0.1, detail=None):
+    """The per-class loop of Inference.infer_gpu (framework/inference.py:35-121) for one frame.  Returns
+    (boxes (D, 7) fp32, scores (D,) fp32, class index (D,) int32, anchor index (D,) int64) in the order of the
+    reference's concatenated lists.  `detail`, if a list, receives one dict per class with the intermediate arrays."""
+    anchors = np.asarray(anchors, np.float32)
+    out_b, out_s, out_c, out_a = [], [], [], []
+    for c, (lo, hi) in enumerate(class_ranges):
+        a_mask = None if anchors_mask is None else np.asarray(anchors_mask)[lo:hi]
+        sel, top_scores = post_select(np.asarray(cls_preds)[lo:hi], a_mask, score_threshold, pre_max)
+        info = dict(sel=sel, scores=top_scores)
+        if detail is not None:
+            detail.append(info)
+        if len(sel) == 0:
+            continue
+        enc = np.asarray(box_preds, np.float32)[lo:hi][sel]
+        d = np.asarray(dir_preds, np.float32)[lo:hi][sel]
+        dir_labels = (d[:, 1] > d[:, 0])                                  # torch.max(dim=-1)[1]: first maximum on a tie
+        boxes = box_decode(enc, anchors[lo:hi][sel])
+        standup = standup_boxes(boxes[:, [0, 1, 3, 4, 6]])
+        # the boxes are already in their final order; strictly decreasing stand-in scores make nms_gpu's argsort keep it
+        rank = np.arange(len(sel), 0, -1).astype(np.float32)
+        selected = nms(standup, rank, pre_max, post_max, iou_threshold)
+        info.update(boxes=boxes.copy(), standup=standup, dir=dir_labels.astype(np.int32),
+                    keep=np.zeros(0, np.int64) if selected is None else selected)
+        if selected is None:
+            continue
+        boxes, scores_kept, range_mask = post_finish(boxes, top_scores, dir_labels, selected, center_limit)
+        out_b.append(boxes)
+        out_s.append(scores_kept)
+        out_c.append(np.full(len(boxes), c, np.int32))
+        out_a.append(lo + sel[selected][range_mask])
+    if not out_b:
+        return (np.zeros((0, 7), np.float32), np.zeros((0,), np.float32), np.zeros((0,), np.int32), np.zeros((0,), np.int64))
+    return (np.concatenate(out_b).astype(np.float32), np.concatenate(out_s).astype(np.float32), np.concatenate(out_c),
+            np.concatenate(out_a).astype(np.int64))
+
+
+def post_min_iou_gap(standup, iou_threshold):
+    """Smallest |IoU - threshold| over all pairs of standup boxes (how far a case is from a float-sensitive decision)."""
+    if len(standup) < 2:
+        return np.inf
+    iou = nms_iou_matrix(standup)
+    iu = np.triu_indices(len(standup), 1)
+    return float(np.abs(iou[iu] - np.float64(np.float32(iou_threshold))).min())

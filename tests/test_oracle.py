@@ -4,7 +4,7 @@ import pytest
 
 from oracle import oracle, spec_parallel
 from tests import util
-from tests.util import cfgmod
+from tests.util import cfgmod, synth
 
 
 @pytest.mark.parametrize("gkey", util.GRID_KEYS)
@@ -206,3 +206,44 @@ def test_nms_oracle_matches_reference_golden(name):
     k = oracle.nms(dets[:, :4], dets[:, 4], 1000, 5, thresh)
     assert k.dtype == np.int64 and k.tolist() == want.tolist()[:5]
     assert oracle.nms(dets[:0, :4], dets[:0, 4], 1000, 300, thresh) is None
+
+
+# ---- detection post-processing (row N4 around the NMS) ---------------------------------------------------------------
+
+POST_CASES = util.POST_CASES
+_post_golden = util.load_post
+
+
+@pytest.mark.parametrize("name", POST_CASES)
+def test_postprocess_oracle_matches_reference(name):
+    """oracle.postprocess_frame against the annotations of the reference's own Inference.infer_gpu
+    (oracle/make_golden_post.py): same detections in the same order, boxes bit-exact (the restatement runs the same numpy
+    operations in the same container), scores to 1 ulp (the reference's sigmoid is torch's, the oracle's numpy's)."""
+    g = _post_golden(name)
+    b, s, c, a = oracle.postprocess_frame(g["cls_preds"][0], g["box_preds"][0], g["dir_preds"][0], g["anchors_mask"][0],
+                                          g["anchors"], g["class_ranges"].tolist(), g["center_limit"].tolist(), 0.05,
+                                          int(g["pre_max"]), int(g["post_max"]), 0.1)
+    names = [str(g["detect_class"][k]) for k in c]
+    assert names == [str(x) for x in g["name"]]
+    want = np.concatenate([g["location"], g["dimensions"], g["rotation_y"].reshape(-1, 1)], 1).astype(np.float32)
+    assert np.array_equal(b.view(np.uint32), want.view(np.uint32)), "boxes are not bit-identical to the reference's"
+    assert np.allclose(s, g["score"], rtol=2e-7, atol=0)
+    assert len(b) > 0
+
+
+def test_postprocess_cases_exercise_the_branches():
+    """The committed cases cover what they are named for."""
+    g = _post_golden("topk")
+    detail = []
+    oracle.postprocess_frame(g["cls_preds"][0], g["box_preds"][0], g["dir_preds"][0], g["anchors_mask"][0], g["anchors"],
+                             g["class_ranges"].tolist(), g["center_limit"].tolist(), 0.05, int(g["pre_max"]),
+                             int(g["post_max"]), 0.1, detail=detail)
+    assert all(len(d["sel"]) == int(g["pre_max"]) for d in detail)          # more candidates than pre_max in every class
+    assert any(len(d["keep"]) == int(g["post_max"]) for d in detail)        # and the post_max cut is reached
+    g = _post_golden("range")
+    detail = []
+    b = oracle.postprocess_frame(g["cls_preds"][0], g["box_preds"][0], g["dir_preds"][0], g["anchors_mask"][0], g["anchors"],
+                                 g["class_ranges"].tolist(), g["center_limit"].tolist(), 0.05, 1000, 300, 0.1, detail=detail)[0]
+    assert 0 < len(b) < sum(len(d["keep"]) for d in detail)                 # the range mask drops some kept boxes
+    g = _post_golden("empty_class")
+    assert "pedestrian" not in [str(x) for x in g["name"]]

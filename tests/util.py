@@ -83,3 +83,45 @@ def load_extra(name):
 def load_anchor(name):
     z = np.load(GOLD / f"anchor_{name}.npz")
     return {k: z[k] for k in z.files}
+
+
+def post_standup_tol(boxes):
+    """Tolerance of a standup-box coordinate: the corners are centre + rotated half sizes, each a few ulp of exp / sin /
+    cos away from numpy's -> 2e-6 relative to the largest operand."""
+    b = np.abs(np.asarray(boxes, np.float64))
+    return 2e-6 * np.maximum(1.0, b[:, [0, 1, 3, 4]].max(axis=1))
+
+
+def assert_post_boxes_close(got, want, what="", final=False):
+    """Decoded boxes (x, y, z, l, w, h, r): x, y and r are exact fp32 restatements of the numpy arithmetic (bit-exact);
+    l, w, h go through exp (2e-6 relative) and z subtracts h / 2 (2e-6 of the larger operand)."""
+    got, want = np.asarray(got), np.asarray(want)
+    assert got.shape == want.shape, f"{what}: shape {got.shape} != {want.shape}"
+    for col in (0, 1, 6):
+        assert np.array_equal(got[:, col].view(np.uint32), np.ascontiguousarray(want[:, col]).view(np.uint32)), \
+            f"{what}: column {col} is not bit-exact"
+    w64 = want.astype(np.float64)
+    assert np.all(np.abs(got[:, 3:6] - w64[:, 3:6]) <= 2e-6 * np.abs(w64[:, 3:6])), f"{what}: dimensions out of tolerance"
+    ztol = 2e-6 * np.maximum(1.0, np.maximum(np.abs(w64[:, 2]), np.abs(w64[:, 5])))
+    assert np.all(np.abs(got[:, 2] - w64[:, 2]) <= ztol), f"{what}: z out of tolerance"
+
+
+POST_CASES = ["small", "topk", "range", "empty_class", "full20"]
+
+
+def load_post(name):
+    """Reference-made vectors of the detection post-processing (oracle/make_golden_post.py).  The full-size case
+    commits hashes instead of 100 MB of inputs: they are regenerated from the seed and must hash the same."""
+    import pytest
+    z = np.load(GOLD / f"post_{name}.npz")
+    g = {k: z[k] for k in z.files}
+    if "anchors" not in g:
+        cfg = cfgmod.builtin_config("20cm")
+        anchors, ranges = synth.anchors_3d(cfgmod.derive_grid(cfg), tuple(int(x) for x in g["feature_map"]))
+        cls, box, dirp, mask = synth.post_preds(1, len(anchors), int(g["seed"]), mean_logit=float(g["mean_logit"]))
+        assert np.array_equal(np.asarray(ranges), g["class_ranges"])
+        for key, arr in (("sha_anchors", anchors), ("sha_cls", cls), ("sha_box", box), ("sha_dir", dirp), ("sha_mask", mask)):
+            if sha(arr) != str(g[key]):
+                pytest.skip(f"synthetic {key[4:]} not bit-identical on this host (numpy stream / libm differs); hash pin not applicable")
+        g.update(anchors=anchors, cls_preds=cls, box_preds=box, dir_preds=dirp, anchors_mask=mask)
+    return g
