@@ -113,7 +113,9 @@ class PostProcessor:
         end = int(offs[idx + 1]) if idx + 1 < len(_lib.POST_REGION_NAMES) else total
         raw = self.scratch[int(offs[idx]):end]
         t = raw.view(getattr(torch, dtype))
-        return t.view(-1, width) if width > 1 else t
+        if width > 1:       # regions are padded to 256 bytes: drop the partial row at the end
+            t = t[:t.numel() // width * width].view(-1, width)
+        return t
 
 
 class Inference:

@@ -126,6 +126,70 @@ def test_c_abi_argument_validation_needs_no_device():
     assert L.pf_anchor_mask(None, 3, None, 0, 0, 0, 8, 8, None, 0, None, None, None) == 0
 
 
+def test_postprocess_abi_validation_and_refusal(pf):
+    """pf_postprocess / pf_post_scratch_*: bad descriptors are rejected without a device; the scratch layout is ordered
+    and 256-byte aligned; the Python mirror refuses to run without a device or on config['device'] = 'cpu'."""
+    import torch
+    Lm = importlib.import_module("3d_object_detection_b200._lib")
+    L = Lm.load()
+    lim = [-80, -80, -10, 80, 80, 10]
+    good = Lm.make_post_desc([[0, 100], [100, 150]], 1, 1000, 300, 0.05, 0.1, lim)
+    one = ctypes.c_void_p(256)
+    bad = [
+        (Lm.make_post_desc([[0, 100], [50, 150]], 1, 1000, 300, 0.05, 0.1, lim), 150, "overlap"),
+        (Lm.make_post_desc([[0, 100], [100, 151]], 1, 1000, 300, 0.05, 0.1, lim), 150, "class_range"),
+        (Lm.make_post_desc([[0, 100]], 1, 4097, 300, 0.05, 0.1, lim), 150, "pre_max"),
+        (Lm.make_post_desc([[0, 100]], 1, 1000, 1025, 0.05, 0.1, lim), 150, "post_max"),
+        (Lm.make_post_desc([[0, 100]], 0, 1000, 300, 0.05, 0.1, lim), 150, "n_cls_channels"),
+    ]
+    for d, A, needle in bad:
+        assert L.pf_post_scratch_bytes(ctypes.byref(d), 1, A) == 0, needle
+        assert needle.encode() in L.pf_last_error_string(), (needle, L.pf_last_error_string())
+        assert L.pf_postprocess(ctypes.byref(d), one, one, one, None, one, 1, A, one, one, one, one, None, one, None) < 0
+    assert L.pf_postprocess(ctypes.byref(good), one, one, one, None, one, 1, 150, None, one, one, one, None, one, None) < 0
+    assert b"scratch" in L.pf_last_error_string()
+    assert L.pf_postprocess(ctypes.byref(good), one, one, one, None, one, 1, 150, one, None, one, one, None, one, None) < 0
+    assert L.pf_postprocess(ctypes.byref(good), one, one, one, None, one, 0, 150, None, None, None, None, None, None, None) == 0
+    offs = (ctypes.c_size_t * len(Lm.POST_REGION_NAMES))()
+    total = L.pf_post_scratch_layout(ctypes.byref(good), 8, 150, offs)
+    o = list(offs)
+    assert o[0] == 0 and o == sorted(o) and all(x % 256 == 0 for x in o) and total > o[-1]
+    assert total == L.pf_post_scratch_bytes(ctypes.byref(good), 8, 150)
+    assert o[1] - o[0] >= 8 * 150 * 8 and total - o[-1] >= L.pf_nms_scratch_bytes(16, 1000)
+    with pytest.raises(ValueError):
+        Lm.make_post_desc([[0, 1]] * 9, 1, 1000, 300, 0.05, 0.1, lim)
+    inf = importlib.import_module("3d_object_detection_b200.inference")
+
+    class A_:
+        anchors = np.zeros((150, 7), np.float32)
+        class_masks = {"vehicle": [0, 100], "pedestrian": [100, 150]}
+    with pytest.raises(pf.PillarFrontError):
+        inf.Inference(dict(device="cpu", center_limit=lim, detect_class=["vehicle", "pedestrian"]), A_())
+    if not torch.cuda.is_available():
+        with pytest.raises(pf.PillarFrontError):
+            inf.PostProcessor(A_.anchors, [[0, 100], [100, 150]], lim)
+        i = inf.Inference(dict(device=0, center_limit=lim, detect_class=["vehicle", "pedestrian"]), A_())
+        assert (i._nms_pre_max_size, i._nms_post_max_size, i._nms_iou_threshold, i._nms_score_threshold) == (1000, 300, 0.1, 0.05)
+        with pytest.raises(pf.PillarFrontError):
+            i.infer_gpu({}, dict(cls_preds=torch.zeros(1, 150, 1), box_preds=torch.zeros(1, 150, 7), dir_preds=torch.zeros(1, 150, 2)))
+    anno = inf.get_start_result_anno()
+    assert set(anno) == {"name", "truncated", "occluded", "alpha", "bbox", "dimensions", "location", "rotation_y", "score"}
+    assert anno["bbox"].shape == (0, 4) and anno["location"].shape == (0, 3)
+
+
+def test_synthetic_anchors_3d_layout():
+    """synth.anchors_3d lays the anchors out like AnchorAssigner (all cells of one size / yaw contiguously, x slow) and
+    its class ranges tile the anchor array; the full-size golden case pins it to the reference's own array by hash."""
+    geom = cfgmod.derive_grid(cfgmod.builtin_config("20cm"))
+    synth = importlib.import_module("3d_object_detection_b200.synth")
+    a, ranges = synth.anchors_3d(geom, (6, 5))
+    assert a.shape == (6 * 5 * 9, 7) and a.dtype == np.float32
+    assert ranges == [[0, 180], [180, 210], [210, 270]]
+    assert np.all(a[:30, 3:6] == np.float32([4.6, 2.1, 1.8])) and np.all(a[:30, 6] == 0) and np.all(a[30:60, 6] == np.float32(np.pi / 2))
+    assert a[0, 0] == a[4, 0] and a[0, 1] != a[1, 1] and a[5, 0] != a[0, 0]          # y fast, x slow
+    assert np.allclose(a[:, 2], a[:, 5] / 2)
+
+
 def test_product_never_imports_oracle():
     for path in (ROOT / "3d_object_detection_b200").rglob("*.py"):
         text = path.read_text()

@@ -1,0 +1,15 @@
+#!/bin/bash
+# the post-processing row on the GPU: its parity tests first, then the probe, then the whole GPU suite
+o=gpurun_out
+mkdir -p $o
+timeout 170 python -m pytest tests/test_gpu_post.py -x -q > $o/post_pytest.log 2>&1
+echo "post tests exit $?" >> $o/post_pytest.log
+tail -25 $o/post_pytest.log
+timeout 60 python tools/post_probe.py --out $o/post_probe.json > $o/post_probe.log 2>&1
+tail -6 $o/post_probe.log
+timeout 60 python -c "import __graft_entry__ as g; g.smoke()" > $o/smoke.log 2>&1
+echo "smoke exit $?" >> $o/smoke.log
+tail -3 $o/smoke.log
+timeout 200 python -m pytest tests -m gpu -x -q > $o/all_pytest.log 2>&1
+echo "all tests exit $?" >> $o/all_pytest.log
+tail -5 $o/all_pytest.log
