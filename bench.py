@@ -46,6 +46,7 @@ def parse_args():
     ap.add_argument("--no-single", action="store_true", help="skip the single-frame drop-in latency measurement")
     ap.add_argument("--no-pfn", action="store_true", help="skip the fused-vs-torch PFN side measurement")
     ap.add_argument("--no-anchor-mask", action="store_true", help="skip the anchor-mask (row N2) side measurement")
+    ap.add_argument("--no-postprocess", action="store_true", help="skip the detection post-processing (row N4) side measurement")
     ap.add_argument("--e2e-eager", action="store_true", help="e2e arm: launch every copy / kernel eagerly instead of one graph per pipeline")
     ap.add_argument("--no-affinity", action="store_true",
                     help="do not pin the rank to the host cores NVML reports as local to its GPU (NUMA-local pinned buffers)")
@@ -379,6 +380,42 @@ def run_b200(args, rank, world, local):
                           "four-corner lookup, mask (frames, anchors) bool left on the device"}
         del am, mask_d
 
+    # ---------------- next-row N4: detection post-processing of the batch (score mask, top-k, decode, NMS, range mask) --
+    post = None
+    if rank == 0 and not args.no_postprocess:
+        try:
+            synth = importlib.import_module("3d_object_detection_b200.synth")
+            imod = importlib.import_module("3d_object_detection_b200.inference")
+            fmap = (int(geom.grid_size[0]) // 2, int(geom.grid_size[1]) // 2)
+            anchors3, ranges3 = synth.anchors_3d(geom, fmap)
+            lim = [float(x) for x in cfg.get("center_limit", [-80.0, -80.0, -10.0, 80.0, 80.0, 10.0])]
+            Bp = max(1, min(B, 8, 12_000_000 // len(anchors3)))       # bounds the host time spent generating head outputs
+            pp = imod.PostProcessor(anchors3, ranges3, lim, max_frames=Bp, device=local)
+            # synthetic head outputs: ~300 anchors per class and frame above the 0.05 score threshold ("sparse", a trained
+            # head) and ~6 % of all anchors ("dense"); random-init heads have no meaningful population of their own
+            post = {"anchors": len(anchors3), "frames": Bp, "launches": 7}
+            for label, mean_logit in (("sparse", -9.6), ("dense", -6.0)):
+                ins = [torch.from_numpy(x).to(dev) for x in synth.post_preds(Bp, len(anchors3), 7, mean_logit=mean_logit)]
+                for _ in range(3):
+                    pp(*ins)
+                torch.cuda.synchronize(dev)
+                a0, a1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+                n_pp = max(5, min(K, 40))
+                a0.record()
+                for _ in range(n_pp):
+                    pp(*ins)
+                a1.record()
+                torch.cuda.synchronize(dev)
+                post[label] = {"ms_per_batch": a0.elapsed_time(a1) / n_pp,
+                               "detections_per_frame": float(pp.det_num[:Bp].float().mean().item())}
+                del ins
+            post["note"] = ("pf_postprocess: anchor mask + sigmoid + score mask -> candidate lists, radix select + bitonic "
+                            "sort of the top 1000 per class and frame, box decode + standup boxes, NMS, direction flip + "
+                            "range mask; detections left on the device")
+            del pp
+        except Exception as exc:      # a side measurement must not take the headline down with it
+            post = {"error": f"{type(exc).__name__}: {exc}"}
+
     # ---------------- drop-in single-frame latency: the reference's own call sequence (InferData.get + forward) -------
     single = None
     if rank == 0 and not args.no_single:
@@ -487,7 +524,7 @@ def run_b200(args, rank, world, local):
         dist.barrier()
         dist.destroy_process_group()
     return dict(cfg=cfg, geom=geom, frames=frames, B=B, K=K, W=W, t_dev=t_dev, t_e2e=t_e2e, t_vox=t_vox,
-                t_scat=t_scat, with_pfn=with_pfn, anchor=anchor, single=single, bound=bound, w_e2e=w_e2e, t_serial=t_serial, d_dev=d_dev, counts=counts, bytes_alg=bytes_alg, n_points=n_points, tot_pts=tot_pts,
+                t_scat=t_scat, with_pfn=with_pfn, anchor=anchor, post=post, single=single, bound=bound, w_e2e=w_e2e, t_serial=t_serial, d_dev=d_dev, counts=counts, bytes_alg=bytes_alg, n_points=n_points, tot_pts=tot_pts,
                 tot_frames=tot_frames, clocks=clocks, h2d=h2d, d2h=d2h, fe=fe, depth=depth, world=world)
 
 
@@ -556,6 +593,7 @@ def main():
         "host_binding": {"cores": len(r["bound"]), "first": r["bound"][0], "last": r["bound"][-1]} if r["bound"] else None,
         "with_pfn": r["with_pfn"],
         "anchor_mask": r["anchor"],
+        "postprocess": r["post"],
         "single_frame_api": r["single"],
         "e2e_hbm_frac": r["bytes_alg"]["e2e"] / (r["t_dev"] / K) / 1e9 / peak,
         "e2e_hbm_frac_serial": r["bytes_alg"]["e2e"] / (r["t_serial"] / K) / 1e9 / peak,

@@ -13,3 +13,5 @@ tail -3 $o/smoke.log
 timeout 200 python -m pytest tests -m gpu -x -q > $o/all_pytest.log 2>&1
 echo "all tests exit $?" >> $o/all_pytest.log
 tail -5 $o/all_pytest.log
+timeout 150 python bench.py --steps 50 --warmup 5 --no-cpu-baseline > $o/bench_post.json 2> $o/bench_post.err
+tail -c 1500 $o/bench_post.json
