@@ -134,7 +134,7 @@ def run_case(pf, fmap, B, seed, mean_logit, pre_max, post_max, with_mask=True, l
     ((40, 40), 2, 33, 2.0, 256, 100, False),        # nearly every anchor is a candidate, no anchor mask
     ((64, 64), 4, 34, -6.0, 1000, 300, True),
     ((8, 8), 2, 35, -12.0, 1000, 300, True),        # almost no candidates; empty segments
-    ((100, 100), 2, 36, 0.0, 4096, 1024, True),     # the largest sizes the ABI admits
+    ((100, 100), 1, 36, 0.0, 4096, 1024, True),     # the largest sizes the ABI admits
 ])
 def test_stagewise_against_oracle(pf, fmap, B, seed, mean_logit, pre_max, post_max, with_mask):
     _, (n_sel, n_keep, n_det), _ = run_case(pf, fmap, B, seed, mean_logit, pre_max, post_max, with_mask)
