@@ -452,6 +452,7 @@ int pf_postprocess(const pf_post_desc *d, const float *cls_preds, const float *b
     k.pre_max = d->pre_max;
     k.post_max = d->post_max;
     k.score_thr = d->score_threshold;
+    pf::post::set_prefilter(k);
     for (int i = 0; i < 6; ++i) k.limit[i] = d->center_limit[i];
     cudaError_t e = pf::launch_postprocess(k, d->iou_threshold, cls_preds, box_preds, dir_preds, anchors_mask, anchors, n_frames,
                                            n_anchors, scratch, det_boxes, det_scores, det_class, det_anchor, det_num,

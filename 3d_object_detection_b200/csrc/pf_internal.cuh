@@ -123,6 +123,9 @@ cudaError_t launch_nms(const float *boxes, const float *scores, const int32_t *s
                        int max_seg, float thresh, int post_max, void *scratch, int32_t *keep, int32_t *keep_num,
                        cudaStream_t stream);
 
+void nms_presorted_views(void *scratch, int n_seg, int max_seg, float **sorted_boxes, int32_t **order);
+cudaError_t launch_nms_presorted(const int32_t *seg_offsets, int n_seg, long long n_total, int max_seg, float thresh,
+                                 int post_max, void *scratch, int32_t *keep, int32_t *keep_num, cudaStream_t stream);
 size_t post_scratch_layout(int n_classes, int pre_max, int post_max, int n_frames, long long n_anchors, size_t *offsets);
 cudaError_t launch_postprocess(const post::Desc &d, float iou_threshold, const float *cls_preds, const float *box_preds,
                                const float *dir_preds, const uint8_t *anchors_mask, const float *anchors, int n_frames,

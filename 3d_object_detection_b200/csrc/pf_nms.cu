@@ -213,30 +213,71 @@ size_t nms_scratch_bytes(int n_seg, int max_seg)
     return rows * sizeof(float4) + rows * sizeof(int32_t) + rows * cb * sizeof(unsigned long long) + 512;
 }
 
-cudaError_t launch_nms(const float *boxes, const float *scores, const int32_t *seg_offsets, int n_seg, long long n_total,
-                       int max_seg, float thresh, int post_max, void *scratch, int32_t *keep, int32_t *keep_num,
-                       cudaStream_t stream)
+namespace {
+
+struct NmsViews {
+    float4 *sboxes;
+    unsigned long long *mask;
+    int32_t *order;
+    int cb;
+};
+
+NmsViews nms_views(void *scratch, int n_seg, int max_seg)
 {
     const size_t rows = (size_t)n_seg * max_seg;
-    const int cb = (max_seg + kNmsTile - 1) / kNmsTile;
+    NmsViews v;
+    v.cb = (max_seg + kNmsTile - 1) / kNmsTile;
     char *base = static_cast<char *>(scratch);
-    float4 *sboxes = reinterpret_cast<float4 *>(base);
-    unsigned long long *mask = reinterpret_cast<unsigned long long *>(base + ((rows * sizeof(float4) + 255) & ~(size_t)255));
-    int32_t *order = reinterpret_cast<int32_t *>(reinterpret_cast<char *>(mask) + ((rows * cb * 8 + 255) & ~(size_t)255));
-    int npad = 1;
-    while (npad < max_seg) npad <<= 1;
-    k_nms_sort<<<n_seg, kNmsSortThreads, (size_t)npad * 8, stream>>>(boxes, scores, seg_offsets, n_total, max_seg, order,
-                                                                    sboxes);
-    k_nms_mask<<<dim3(cb, cb, n_seg), kNmsTile, 0, stream>>>(sboxes, seg_offsets, n_total, max_seg, cb, thresh, mask);
+    v.sboxes = reinterpret_cast<float4 *>(base);
+    v.mask = reinterpret_cast<unsigned long long *>(base + ((rows * sizeof(float4) + 255) & ~(size_t)255));
+    v.order = reinterpret_cast<int32_t *>(reinterpret_cast<char *>(v.mask) + ((rows * v.cb * 8 + 255) & ~(size_t)255));
+    return v;
+}
+
+// overlap mask + greedy walk on sorted boxes (v.sboxes / v.order filled by k_nms_sort or by the caller)
+cudaError_t launch_mask_scan(const NmsViews &v, const int32_t *seg_offsets, int n_seg, long long n_total, int max_seg,
+                             float thresh, int post_max, int32_t *keep, int32_t *keep_num, cudaStream_t stream)
+{
+    k_nms_mask<<<dim3(v.cb, v.cb, n_seg), kNmsTile, 0, stream>>>(v.sboxes, seg_offsets, n_total, max_seg, v.cb, thresh, v.mask);
     // shared-memory staging of the mask: up to 200 KB (opt-in above 48 KB)
     constexpr int kScanSmem = 200 * 1024;
     cudaError_t e = cudaFuncSetAttribute(k_nms_scan, cudaFuncAttributeMaxDynamicSharedMemorySize, kScanSmem);   // per device
     if (e != cudaSuccess) return e;
-    const long long need = (long long)max_seg * cb * 8;
+    const long long need = (long long)max_seg * v.cb * 8;
     const int smem = (int)(need < kScanSmem ? need : kScanSmem);
-    k_nms_scan<<<n_seg, kNmsScanThreads, smem, stream>>>(mask, order, seg_offsets, n_total, max_seg, cb, post_max, smem / 8,
-                                                        keep, keep_num);
+    k_nms_scan<<<n_seg, kNmsScanThreads, smem, stream>>>(v.mask, v.order, seg_offsets, n_total, max_seg, v.cb, post_max,
+                                                        smem / 8, keep, keep_num);
     return cudaGetLastError();
+}
+
+}  // namespace
+
+cudaError_t launch_nms(const float *boxes, const float *scores, const int32_t *seg_offsets, int n_seg, long long n_total,
+                       int max_seg, float thresh, int post_max, void *scratch, int32_t *keep, int32_t *keep_num,
+                       cudaStream_t stream)
+{
+    const NmsViews v = nms_views(scratch, n_seg, max_seg);
+    int npad = 1;
+    while (npad < max_seg) npad <<= 1;
+    k_nms_sort<<<n_seg, kNmsSortThreads, (size_t)npad * 8, stream>>>(boxes, scores, seg_offsets, n_total, max_seg, v.order,
+                                                                    v.sboxes);
+    return launch_mask_scan(v, seg_offsets, n_seg, n_total, max_seg, thresh, post_max, keep, keep_num, stream);
+}
+
+// Where a caller that already holds its boxes in NMS order writes them instead of running the sort: sorted boxes
+// [n_seg][max_seg][4] and the index each one reports when kept [n_seg][max_seg].
+void nms_presorted_views(void *scratch, int n_seg, int max_seg, float **sorted_boxes, int32_t **order)
+{
+    const NmsViews v = nms_views(scratch, n_seg, max_seg);
+    *sorted_boxes = reinterpret_cast<float *>(v.sboxes);
+    *order = v.order;
+}
+
+cudaError_t launch_nms_presorted(const int32_t *seg_offsets, int n_seg, long long n_total, int max_seg, float thresh,
+                                 int post_max, void *scratch, int32_t *keep, int32_t *keep_num, cudaStream_t stream)
+{
+    return launch_mask_scan(nms_views(scratch, n_seg, max_seg), seg_offsets, n_seg, n_total, max_seg, thresh, post_max, keep,
+                            keep_num, stream);
 }
 
 }  // namespace pf

@@ -1,5 +1,6 @@
-// Launch side of the detection post-processing (pf_postprocess): score -> select -> decode -> pf_nms -> finish.
-// Kernel bodies and the reference lines they follow: pf_post_kernels.cuh.  Seven launches and one 4-byte-per-segment
+// Launch side of the detection post-processing (pf_postprocess): score -> select -> decode -> NMS (overlap mask + greedy
+// walk of pf_nms.cu; its sort is skipped, the decode kernel emits the boxes in NMS order) -> finish.
+// Kernel bodies and the reference lines they follow: pf_post_kernels.cuh.  Six launches and one 4-byte-per-segment
 // memset per batch, nothing synchronises or allocates, so the whole call can be captured into a CUDA graph.
 #include "pf_internal.cuh"
 #include "pf_post_kernels.cuh"
@@ -63,13 +64,21 @@ cudaError_t launch_postprocess(const post::Desc &d, float iou_threshold, const f
     int *keep = reinterpret_cast<int *>(at(PF_POST_KEEP));
     int *keep_num = reinterpret_cast<int *>(at(PF_POST_KEEP_NUM));
     const int S = n_frames * d.n_classes;
+    float *nms_boxes;
+    int32_t *nms_order;
+    nms_presorted_views(at(PF_POST_NMS_SCRATCH), S, d.pre_max, &nms_boxes, &nms_order);
 
     cudaError_t e = cudaMemsetAsync(cand_count, 0, (size_t)S * 4, stream);
     if (e != cudaSuccess) return e;
     const int per_block = post::kScoreThreads * post::kScorePerThread;
     if (n_anchors > 0) {
         const dim3 grid((unsigned)((n_anchors + per_block - 1) / per_block), (unsigned)n_frames);
-        post::k_post_score<<<grid, post::kScoreThreads, 0, stream>>>(d, cls_preds, anchors_mask, n_anchors, cand, cand_count);
+        const bool vec = d.n_ch == 1 && n_anchors % 4 == 0 && (reinterpret_cast<uintptr_t>(cls_preds) & 15) == 0 &&
+                         (reinterpret_cast<uintptr_t>(anchors_mask) & 3) == 0;
+        if (vec)
+            post::k_post_score<true><<<grid, post::kScoreThreads, 0, stream>>>(d, cls_preds, anchors_mask, n_anchors, cand, cand_count);
+        else
+            post::k_post_score<false><<<grid, post::kScoreThreads, 0, stream>>>(d, cls_preds, anchors_mask, n_anchors, cand, cand_count);
     }
     int npad = 1;
     while (npad < d.pre_max) npad <<= 1;
@@ -77,12 +86,12 @@ cudaError_t launch_postprocess(const post::Desc &d, float iou_threshold, const f
     const dim3 dgrid((unsigned)((d.pre_max + post::kDecodeThreads - 1) / post::kDecodeThreads), (unsigned)S);
     post::k_post_decode<<<dgrid, post::kDecodeThreads, 0, stream>>>(d, n_anchors, S, sel_key, sel_num, box_preds, dir_preds,
                                                                     anchors, seg_offsets, sel_anchor, sel_score, sel_box,
-                                                                    sel_standup, sel_dir, sel_rank);
+                                                                    sel_standup, sel_dir, sel_rank, nms_boxes, nms_order);
     e = cudaGetLastError();
     if (e != cudaSuccess) return e;
-    // the boxes are already in their final order: sel_rank decreases strictly along it, so pf_nms's sort is the identity
-    e = launch_nms(sel_standup, sel_rank, seg_offsets, S, (long long)S * d.pre_max, d.pre_max, iou_threshold, d.post_max,
-                   at(PF_POST_NMS_SCRATCH), keep, keep_num, stream);
+    // the boxes are already in their final order (k_post_decode wrote them where pf_nms's sort would have): mask + walk only
+    e = launch_nms_presorted(seg_offsets, S, (long long)S * d.pre_max, d.pre_max, iou_threshold, d.post_max,
+                             at(PF_POST_NMS_SCRATCH), keep, keep_num, stream);
     if (e != cudaSuccess) return e;
     post::k_post_finish<<<n_frames, post::kFinishThreads, 0, stream>>>(d, seg_offsets, keep, keep_num, sel_box, sel_score,
                                                                        sel_dir, sel_anchor, det_boxes, det_scores, det_class,

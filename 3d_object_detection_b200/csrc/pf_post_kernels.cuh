@@ -93,8 +93,12 @@ PF_DEV int class_of(const Desc &d, int a)
 PF_DEV unsigned long long make_key(float logit, int local) { return ((unsigned long long)orderable(logit) << 32) | (unsigned int)~(unsigned int)local; }
 
 // ---- 1. score: anchor mask, max logit over the class channels, score threshold, candidate lists per (frame, class) ----
-// grid (ceil(A / (256 * 4)), n_frames).  cand holds n_frames * A keys: segment (f, c) owns [f * A + lo[c], f * A + hi[c]).
-// cand_count [n_frames * n_classes] must be zero on entry.
+// grid (ceil(A / (256 * 4)), n_frames); a thread owns 4 consecutive anchors.  VEC (one class channel, A % 4 == 0, aligned
+// pointers): one 16-byte load of the logits and one 4-byte load of the mask per thread.  The exact test is
+// sigmoid(logit) >= threshold; logits outside [logit_lo, logit_hi] (the threshold's logit -+ 2e-3, far more than the few
+// ulp a computed sigmoid can be off) are decided without evaluating it, which is almost all of them.
+// cand holds n_frames * A keys: segment (f, c) owns [f * A + lo[c], f * A + hi[c]).  cand_count must be zero on entry.
+template <bool VEC>
 __global__ void __launch_bounds__(kScoreThreads)
 k_post_score(Desc d, const float *__restrict__ cls, const uint8_t *__restrict__ amask, long long A,
              unsigned long long *__restrict__ cand, int *__restrict__ cand_count)
@@ -103,31 +107,51 @@ k_post_score(Desc d, const float *__restrict__ cls, const uint8_t *__restrict__ 
     const int f = blockIdx.y, tid = threadIdx.x;
     if (tid < kMaxClasses) s_cnt[tid] = 0;
     __syncthreads();
-    const long long a0 = (long long)blockIdx.x * (kScoreThreads * kScorePerThread) + tid;
+    const long long a0 = ((long long)blockIdx.x * kScoreThreads + tid) * kScorePerThread;
+    float logit[kScorePerThread];
+    bool ok[kScorePerThread];
+    if (VEC) {
+        const bool in = a0 < A;                       // A % 4 == 0: the four anchors are in range together
+        float4 v = {0.f, 0.f, 0.f, 0.f};
+        uchar4 m = {1, 1, 1, 1};
+        if (in) {
+            v = *reinterpret_cast<const float4 *>(cls + (long long)f * A + a0);
+            if (amask) m = *reinterpret_cast<const uchar4 *>(amask + (long long)f * A + a0);
+        }
+        logit[0] = v.x, logit[1] = v.y, logit[2] = v.z, logit[3] = v.w;
+        ok[0] = in && m.x, ok[1] = in && m.y, ok[2] = in && m.z, ok[3] = in && m.w;
+    } else {
+#pragma unroll
+        for (int j = 0; j < kScorePerThread; ++j) {
+            const long long a = a0 + j;
+            ok[j] = a < A && (!amask || amask[(long long)f * A + a]);
+            logit[j] = 0.f;
+            if (ok[j]) {
+                const float *p = cls + ((long long)f * A + a) * d.n_ch;
+                float top = p[0];
+                bool nan = top != top;
+                for (int k = 1; k < d.n_ch; ++k) {
+                    const float v = p[k];
+                    nan = nan || v != v;
+                    if (v > top) top = v;
+                }
+                logit[j] = top;
+                ok[j] = !nan;                        // NaN >= threshold is false in the reference as well
+            }
+        }
+    }
     int cl[kScorePerThread], rk[kScorePerThread];
-    unsigned long long key[kScorePerThread];
 #pragma unroll
     for (int j = 0; j < kScorePerThread; ++j) {
-        const long long a = a0 + (long long)j * kScoreThreads;
         cl[j] = -1;
         rk[j] = 0;
-        key[j] = 0;
-        if (a >= A) continue;
-        const int c = class_of(d, (int)a);
+        if (!ok[j]) continue;
+        const float x = logit[j];
+        const bool pass = x > d.logit_hi || (x >= d.logit_lo && sigmoid(x) >= d.score_thr);     // false for NaN
+        if (!pass) continue;
+        const int c = class_of(d, (int)(a0 + j));
         if (c < 0) continue;
-        if (amask && !amask[(long long)f * A + a]) continue;
-        const float *p = cls + ((long long)f * A + a) * d.n_ch;
-        float logit = p[0];
-        bool nan = logit != logit;
-        for (int k = 1; k < d.n_ch; ++k) {
-            const float v = p[k];
-            nan = nan || v != v;
-            if (v > logit) logit = v;
-        }
-        if (nan) continue;                       // NaN >= threshold is false in the reference as well
-        if (!(sigmoid(logit) >= d.score_thr)) continue;
         cl[j] = c;
-        key[j] = make_key(logit, (int)a - d.lo[c]);
         rk[j] = atomicAdd(&s_cnt[c], 1);
     }
     __syncthreads();
@@ -135,12 +159,16 @@ k_post_score(Desc d, const float *__restrict__ cls, const uint8_t *__restrict__ 
     __syncthreads();
 #pragma unroll
     for (int j = 0; j < kScorePerThread; ++j)
-        if (cl[j] >= 0) cand[(long long)f * A + d.lo[cl[j]] + s_base[cl[j]] + rk[j]] = key[j];
+        if (cl[j] >= 0)
+            cand[(long long)f * A + d.lo[cl[j]] + s_base[cl[j]] + rk[j]] = make_key(logit[j], (int)(a0 + j) - d.lo[cl[j]]);
 }
 
 // ---- 2. select: the pre_max largest keys of every segment, sorted descending -------------------------------------------
 // One CTA per segment.  More candidates than pre_max: MSB-first radix select (8 bits a pass) finds the pre_max-th largest
-// key T, then the keys >= T (exactly pre_max of them: keys are unique) are collected.  Bitonic sort in shared memory.
+// key T, then the keys >= T (exactly pre_max of them: keys are unique) are collected.  A pass ends the search as soon as
+// the boundary bin is needed whole (typically once the bits that tell the logits apart are consumed: 3-4 passes).  The
+// upper bits of the keys are nearly constant, so a plain shared-memory histogram would serialise on one bin: each thread
+// counts runs of equal digits in registers and issues one atomic per run.  Bitonic sort in shared memory.
 // dynamic shared memory: npad * 8 bytes, npad = pre_max rounded up to a power of two.
 __global__ void __launch_bounds__(kSelectThreads)
 k_post_select(Desc d, long long A, const unsigned long long *__restrict__ cand, const int *__restrict__ cand_count,
@@ -149,27 +177,38 @@ k_post_select(Desc d, long long A, const unsigned long long *__restrict__ cand, 
     PF_DYN_SHARED(unsigned long long, s_keys);
     __shared__ unsigned int s_hist[256];
     __shared__ unsigned int s_grp[16];
-    __shared__ unsigned long long s_prefix;
-    __shared__ int s_krem, s_n;
+    __shared__ unsigned long long s_prefix, s_T;
+    __shared__ int s_krem, s_n, s_done;
     const int seg = blockIdx.x, tid = threadIdx.x;
     const int f = seg / d.n_classes, c = seg - f * d.n_classes;
     const unsigned long long *src = cand + (long long)f * A + d.lo[c];
     const int M = cand_count[seg];
     const int k = M < d.pre_max ? M : d.pre_max;
     int npad = 1;
-    while (npad < d.pre_max) npad <<= 1;
+    while (npad < k) npad <<= 1;                     // <= pre_max rounded up: the launch's shared memory covers it
     unsigned long long T = 0;
     if (M > d.pre_max) {
-        if (tid == 0) s_prefix = 0, s_krem = k;
+        if (tid == 0) s_prefix = 0, s_krem = k, s_done = 0, s_T = 0;
         for (int pass = 0; pass < 8; ++pass) {
             const int shift = 56 - 8 * pass;
             if (tid < 256) s_hist[tid] = 0;
             __syncthreads();
             const unsigned long long prefix = s_prefix;
+            int run_d = -1;
+            unsigned int run_n = 0;
+#pragma unroll 4
             for (int i = tid; i < M; i += kSelectThreads) {
                 const unsigned long long key = src[i];
-                if (pass == 0 || (key >> (shift + 8)) == prefix) atomicAdd(&s_hist[(unsigned int)(key >> shift) & 255u], 1u);
+                if (pass == 0 || (key >> (shift + 8)) == prefix) {
+                    const int dg = (int)((key >> shift) & 255ull);
+                    if (dg == run_d) ++run_n;
+                    else {
+                        if (run_n) atomicAdd(&s_hist[run_d], run_n);
+                        run_d = dg, run_n = 1;
+                    }
+                }
             }
+            if (run_n) atomicAdd(&s_hist[run_d], run_n);
             __syncthreads();
             if (tid < 16) {
                 unsigned int g = 0;
@@ -183,16 +222,21 @@ k_post_select(Desc d, long long A, const unsigned long long *__restrict__ cand, 
                 while (g > 0 && acc + s_grp[g] < krem) acc += s_grp[g], --g;
                 int b = g * 16 + 15;
                 while (b > g * 16 && acc + s_hist[b] < krem) acc += s_hist[b], --b;
-                s_krem = (int)(krem - acc);
-                s_prefix = (prefix << 8) | (unsigned long long)b;
+                krem -= acc;
+                const unsigned long long next = (prefix << 8) | (unsigned long long)b;
+                if (s_hist[b] == krem || shift == 0) s_T = next << shift, s_done = 1;     // the whole boundary bin is wanted
+                s_krem = (int)krem;
+                s_prefix = next;
             }
             __syncthreads();
+            if (s_done) break;
         }
-        T = s_prefix;
+        T = s_T;
     }
     if (tid == 0) s_n = 0;
     for (int i = tid; i < npad; i += kSelectThreads) s_keys[i] = 0;
     __syncthreads();
+#pragma unroll 4
     for (int i = tid; i < M; i += kSelectThreads) {
         const unsigned long long key = src[i];
         if (key >= T) {
@@ -252,13 +296,15 @@ PF_DEV void decode_one(const float *enc, const float *anc, float *box, float *st
 
 // ---- 3. decode: gather the selected anchors, decode, standup boxes; compact layout for pf_nms ------------------------
 // grid (ceil(pre_max / 128), n_segments).  Outputs are indexed seg_offsets[seg] + rank; seg_offsets [n_seg + 1] is
-// written by block (0, 0).  nms_rank = pre_max - rank: strictly decreasing "scores" that make pf_nms keep this order.
+// written by block (0, 0).  The boxes are already in NMS order, so the kernel also writes what pf_nms's sort would produce
+// (nms_boxes [seg][pre_max] float4 = the standup boxes, nms_order [seg][pre_max] = the identity) and the sort is skipped;
+// out_rank = pre_max - rank is the strictly decreasing "score" that would make pf_nms's own sort keep this order.
 __global__ void __launch_bounds__(kDecodeThreads)
 k_post_decode(Desc d, long long A, int n_seg, const unsigned long long *__restrict__ sel_key, const int *__restrict__ sel_num,
               const float *__restrict__ box_preds, const float *__restrict__ dir_preds, const float *__restrict__ anchors,
               int *__restrict__ seg_offsets, int *__restrict__ out_anchor, float *__restrict__ out_score,
               float *__restrict__ out_box, float *__restrict__ out_standup, int *__restrict__ out_dir,
-              float *__restrict__ out_rank)
+              float *__restrict__ out_rank, float *__restrict__ nms_boxes, int *__restrict__ nms_order)
 {
     __shared__ int s_off;
     const int seg = blockIdx.y, tid = threadIdx.x;
@@ -293,11 +339,14 @@ k_post_decode(Desc d, long long A, int n_seg, const unsigned long long *__restri
 #pragma unroll
     for (int q = 0; q < 7; ++q) out_box[o * 7 + q] = box[q];
 #pragma unroll
-    for (int q = 0; q < 4; ++q) out_standup[o * 4 + q] = su[q];
+    for (int q = 0; q < 4; ++q) out_standup[o * 4 + q] = su[q], nms_boxes[((long long)seg * d.pre_max + i) * 4 + q] = su[q];
+    nms_order[(long long)seg * d.pre_max + i] = i;
 }
 
 // ---- 4. finish: what infer_gpu does with the kept boxes (:97-121), per frame, classes in class_masks order ------------
-// One CTA per frame.  det_* rows of frame f start at f * n_classes * post_max; det_num[f] rows are valid.
+// One CTA per frame walks the kept boxes of all its classes as one list (class-major, NMS order inside a class), 1024 at
+// a time: direction flip, range mask, limit_period, then an ordered compaction through 32 bit-words of pass flags.
+// det_* rows of frame f start at f * n_classes * post_max; det_num[f] rows are valid.
 __global__ void __launch_bounds__(kFinishThreads)
 k_post_finish(Desc d, const int *__restrict__ seg_offsets, const int *__restrict__ keep, const int *__restrict__ keep_num,
               const float *__restrict__ in_box, const float *__restrict__ in_score, const int *__restrict__ in_dir,
@@ -305,19 +354,32 @@ k_post_finish(Desc d, const int *__restrict__ seg_offsets, const int *__restrict
               int *__restrict__ det_class, int *__restrict__ det_anchor, int *__restrict__ det_num)
 {
     __shared__ unsigned char s_flag[kFinishThreads];
-    __shared__ int s_total;
+    __shared__ unsigned int s_word[kFinishThreads / 32];
+    __shared__ int s_start[kMaxClasses + 1];
     const int f = blockIdx.x, tid = threadIdx.x;
     const long long row0 = (long long)f * d.n_classes * d.post_max;
+    if (tid == 0) {
+        int run = 0;
+        for (int c = 0; c < d.n_classes; ++c) {
+            int n = keep_num[f * d.n_classes + c];
+            n = n < 0 ? 0 : (n > d.post_max ? d.post_max : n);
+            s_start[c] = run, run += n;
+        }
+        s_start[d.n_classes] = run;
+    }
+    __syncthreads();
+    const int total = s_start[d.n_classes];
     int base = 0;
-    for (int c = 0; c < d.n_classes; ++c) {
-        const int seg = f * d.n_classes + c;
-        int n = keep_num[seg];
-        n = n < 0 ? 0 : (n > d.post_max ? d.post_max : n);
+    for (int e0 = 0; e0 < total; e0 += kFinishThreads) {
+        const int e = e0 + tid;
         bool pass = false;
         float b[7] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
         long long g = 0;
-        if (tid < n) {
-            g = (long long)seg_offsets[seg] + keep[(long long)seg * d.post_max + tid];
+        int c = 0;
+        if (e < total) {
+            while (e >= s_start[c + 1]) ++c;
+            const int seg = f * d.n_classes + c;
+            g = (long long)seg_offsets[seg] + keep[(long long)seg * d.post_max + (e - s_start[c])];
 #pragma unroll
             for (int q = 0; q < 7; ++q) b[q] = in_box[g * 7 + q];
             // box_preds[..., -1] += np.where(opp_labels, np.pi, 0.0): float64 addend, result cast back to float32
@@ -332,23 +394,27 @@ k_post_finish(Desc d, const int *__restrict__ seg_offsets, const int *__restrict
         }
         s_flag[tid] = pass ? 1 : 0;
         __syncthreads();
-        if (tid == 0) {
-            int t = 0;
-            for (int i = 0; i < n; ++i) t += s_flag[i];
-            s_total = t;
+        if (tid < kFinishThreads / 32) {
+            unsigned int w = 0;
+            for (int q = 0; q < 32; ++q) w |= (unsigned int)s_flag[tid * 32 + q] << q;
+            s_word[tid] = w;
+        }
+        __syncthreads();
+        int before = 0, all = 0;
+        for (int w = 0; w < kFinishThreads / 32; ++w) {
+            const int n = __popc(s_word[w]);
+            all += n;
+            if (w < (tid >> 5)) before += n;
         }
         if (pass) {
-            int pos = 0;
-            for (int i = 0; i < tid; ++i) pos += s_flag[i];
-            const long long o = row0 + base + pos;
+            const long long o = row0 + base + before + __popc(s_word[tid >> 5] & ((1u << (tid & 31)) - 1u));
 #pragma unroll
             for (int q = 0; q < 7; ++q) det_box[o * 7 + q] = b[q];
             det_score[o] = in_score[g];
             det_class[o] = c;
             if (det_anchor) det_anchor[o] = in_anchor[g];
         }
-        __syncthreads();
-        base += s_total;
+        base += all;
         __syncthreads();
     }
     if (tid == 0) det_num[f] = base;

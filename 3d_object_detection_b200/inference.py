@@ -10,7 +10,7 @@ Mirror of the reference's ``framework/inference.py``:
   KITTI fields of ``get_start_result_anno`` :724-737).
 
 The reference walks the classes of ONE frame in Python with ~10 ``torch.cuda.synchronize()`` per class, copies the top-k
-rows to the host, decodes in numpy and runs the numba NMS.  Here a batch of frames x classes goes through seven launches
+rows to the host, decodes in numpy and runs the numba NMS.  Here a batch of frames x classes goes through six launches
 on the device (``PostProcessor``), and the only synchronisation is the final read-back of the detections; a batch of
 more than one frame returns one annotation dict per frame (the reference handles batch 1 only: ``squeeze(0)``).
 

@@ -208,3 +208,16 @@ def post_preds(n_frames: int, n_anchors: int, seed: int, mean_logit: float = -6.
     dirp = rng.normal(0.0, 1.0, (n_frames, n_anchors, 2)).astype(np.float32)
     mask = rng.random((n_frames, n_anchors)) < mask_frac
     return cls, box, dirp, mask
+
+
+def post_threshold_band(cls: np.ndarray, score_threshold: float = 0.05, half_width: float = 0.01, seed: int = 0) -> np.ndarray:
+    """Overwrite the class logits (in place) with values spread over [L - half_width, L + half_width], L = the logit of the
+    score threshold: the region where the score mask is decided by the computed sigmoid itself.  Logits whose fp64 sigmoid
+    lies within 2e-7 of the threshold (where two correct fp32 implementations may disagree) are moved up by half_width / 2."""
+    rng = np.random.default_rng(seed)
+    L = np.log(score_threshold / (1.0 - score_threshold))
+    x = rng.uniform(L - half_width, L + half_width, cls.shape).astype(np.float32)
+    s = 1.0 / (1.0 + np.exp(-x.astype(np.float64)))
+    x[np.abs(s - np.float64(np.float32(score_threshold))) < 2e-7] += np.float32(half_width / 2)
+    cls[...] = x
+    return cls

@@ -393,7 +393,7 @@ def run_b200(args, rank, world, local):
             pp = imod.PostProcessor(anchors3, ranges3, lim, max_frames=Bp, device=local)
             # synthetic head outputs: ~300 anchors per class and frame above the 0.05 score threshold ("sparse", a trained
             # head) and ~6 % of all anchors ("dense"); random-init heads have no meaningful population of their own
-            post = {"anchors": len(anchors3), "frames": Bp, "launches": 7}
+            post = {"anchors": len(anchors3), "frames": Bp, "launches": 6}
             for label, mean_logit in (("sparse", -9.6), ("dense", -6.0)):
                 ins = [torch.from_numpy(x).to(dev) for x in synth.post_preds(Bp, len(anchors3), 7, mean_logit=mean_logit)]
                 for _ in range(3):

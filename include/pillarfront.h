@@ -215,7 +215,7 @@ PF_API int pf_nms(const float *boxes, const float *scores, const int32_t *seg_of
  *   box_decode (framework/box_np_ops.py:406-424), centre boxes -> corners -> standup boxes (box_np_ops.py:81-99,
  *   122-153, 64-78, 899-904), nms (:85-91), direction flip (:97-104), range mask (:106-109), limit_period (:113).
  * The reference does this per frame and class with ~10 device synchronisations, a device->host copy of the top-k
- * rows, numpy decoding, and the numba NMS; here one call handles n_frames * n_classes segments in seven launches.
+ * rows, numpy decoding, and the numba NMS; here one call handles n_frames * n_classes segments in six launches.
  *
  *   cls_preds    device float [n_frames][n_anchors][n_cls_channels]   (logits)
  *   box_preds    device float [n_frames][n_anchors][7]                (x, y, z, l, w, h, r encodings)
@@ -258,7 +258,7 @@ typedef enum pf_post_region {
     PF_POST_SEL_BOX,         /* float rows x 7: decoded boxes                            */
     PF_POST_SEL_STANDUP,     /* float rows x 4: standup boxes handed to the NMS          */
     PF_POST_SEL_DIR,         /* int32 rows: direction label                              */
-    PF_POST_SEL_RANK,        /* float rows: pre_max - rank (the NMS sort key)            */
+    PF_POST_SEL_RANK,        /* float rows: pre_max - rank (decreasing along the order) */
     PF_POST_KEEP,            /* int32 [segments][post_max] kept ranks, -1 padded         */
     PF_POST_KEEP_NUM,        /* int32 [segments]                                         */
     PF_POST_NMS_SCRATCH,

@@ -22,6 +22,14 @@ struct dim3 {
     dim3(unsigned x_ = 1, unsigned y_ = 1, unsigned z_ = 1) : x(x_), y(y_), z(z_) {}
 };
 
+struct float4 {
+    float x, y, z, w;
+};
+struct uchar4 {
+    unsigned char x, y, z, w;
+};
+inline int __popc(unsigned int x) { return __builtin_popcount(x); }
+
 inline thread_local pf_emul_uint3 threadIdx, blockIdx;
 inline thread_local dim3 blockDim, gridDim;
 inline void *pf_emul_dyn_smem = nullptr;

@@ -16,6 +16,7 @@ Desc make_desc(int n_classes, const int *ranges, int n_ch, int pre_max, int post
     for (int c = 0; c < n_classes; ++c) d.lo[c] = ranges[2 * c], d.hi[c] = ranges[2 * c + 1];
     d.n_ch = n_ch, d.pre_max = pre_max, d.post_max = post_max, d.score_thr = thr;
     for (int i = 0; i < 6; ++i) d.limit[i] = limit ? limit[i] : 0.0;
+    set_prefilter(d);
     return d;
 }
 
@@ -27,21 +28,26 @@ extern "C" {
 int emul_post_front(int n_classes, const int *ranges, int n_ch, int pre_max, float thr, const float *cls, const float *box,
                     const float *dir, const uint8_t *amask, const float *anchors, int n_frames, long long A,
                     unsigned long long *cand, int *cand_count, unsigned long long *sel_key, int *sel_num, int *seg_offsets,
-                    int *sel_anchor, float *sel_score, float *sel_box, float *sel_standup, int *sel_dir, float *sel_rank)
+                    int *sel_anchor, float *sel_score, float *sel_box, float *sel_standup, int *sel_dir, float *sel_rank,
+                    float *nms_boxes, int *nms_order, int force_scalar)
 {
     const Desc d = make_desc(n_classes, ranges, n_ch, pre_max, 1, thr, nullptr);
     const int S = n_frames * n_classes;
     for (int s = 0; s < S; ++s) cand_count[s] = 0;
     const int per_block = kScoreThreads * kScorePerThread;
-    if (A > 0)
-        pf_emul_launch(dim3((unsigned)((A + per_block - 1) / per_block), (unsigned)n_frames), kScoreThreads, 0,
-                       [=] { k_post_score(d, cls, amask, A, cand, cand_count); });
+    if (A > 0) {
+        const dim3 grid((unsigned)((A + per_block - 1) / per_block), (unsigned)n_frames);
+        if (n_ch == 1 && A % 4 == 0 && !force_scalar)        // the same choice pf_post.cu makes (host arrays are aligned)
+            pf_emul_launch(grid, kScoreThreads, 0, [=] { k_post_score<true>(d, cls, amask, A, cand, cand_count); });
+        else
+            pf_emul_launch(grid, kScoreThreads, 0, [=] { k_post_score<false>(d, cls, amask, A, cand, cand_count); });
+    }
     int npad = 1;
     while (npad < pre_max) npad <<= 1;
     pf_emul_launch(dim3((unsigned)S), kSelectThreads, (size_t)npad * 8, [=] { k_post_select(d, A, cand, cand_count, sel_key, sel_num); });
     pf_emul_launch(dim3((unsigned)((pre_max + kDecodeThreads - 1) / kDecodeThreads), (unsigned)S), kDecodeThreads, 0, [=] {
         k_post_decode(d, A, S, sel_key, sel_num, box, dir, anchors, seg_offsets, sel_anchor, sel_score, sel_box, sel_standup,
-                      sel_dir, sel_rank);
+                      sel_dir, sel_rank, nms_boxes, nms_order);
     });
     return 0;
 }

@@ -172,6 +172,16 @@ def test_ties_and_special_values(pf):
     assert first[0] == 7
 
 
+def test_score_mask_around_the_threshold(pf):
+    """Logits within 0.01 of the threshold's logit (the kernel evaluates the sigmoid inside +-2e-3 of it and decides by
+    comparison outside): same score mask as the oracle, for the vectorised and the generic score kernel."""
+    def edit(cls, box, dirp, mask):
+        synth.post_threshold_band(cls, 0.05, 0.01, seed=12)
+    post, (n_sel, _, _), (cls, _, _, mask, _, _) = run_case(pf, (48, 48), 2, 52, -3.0, 4096, 300, True, edit=edit)
+    assert 0.3 < n_sel / mask.sum() < 0.7
+    run_case(pf, (47, 47), 1, 53, -3.0, 4096, 300, True, edit=edit)       # 47 * 47 * 9 anchors: A % 4 != 0, generic kernel
+
+
 def test_two_class_channels(pf):
     cfg = util.cfgmod.builtin_config("20cm")
     anchors, ranges = synth.anchors_3d(util.cfgmod.derive_grid(cfg), (24, 24))

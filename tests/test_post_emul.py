@@ -27,7 +27,7 @@ def _p(a):
     return a.ctypes.data_as(C.c_void_p)
 
 
-def run_emul(L, cls, box, dirp, mask, anchors, ranges, limit, thr, pre_max, post_max, iou_thr):
+def run_emul(L, cls, box, dirp, mask, anchors, ranges, limit, thr, pre_max, post_max, iou_thr, force_scalar=0):
     """score + select + decode on the emulated kernels, the oracle's NMS in place of pf_nms (whose kernels use warp
     shuffles and are covered on the GPU), then the emulated finish kernel."""
     B, A = cls.shape[0], cls.shape[1]
@@ -46,11 +46,17 @@ def run_emul(L, cls, box, dirp, mask, anchors, ranges, limit, thr, pre_max, post
     sel_su = np.full((rows, 4), np.nan, np.float32)
     sel_dir = np.full(rows, -7, np.int32)
     sel_rank = np.full(rows, np.nan, np.float32)
+    nms_boxes = np.full((rows, 4), np.nan, np.float32)
+    nms_order = np.full(rows, -7, np.int32)
     m8 = None if mask is None else np.ascontiguousarray(mask, np.uint8)
     L.emul_post_front(C.c_int(nc), _p(rng), C.c_int(cls.shape[2]), C.c_int(pre_max), C.c_float(thr), _p(cls), _p(box), _p(dirp),
                       _p(m8) if m8 is not None else None, _p(anchors), C.c_int(B), C.c_longlong(A), _p(cand), _p(cand_count),
                       _p(sel_key), _p(sel_num), _p(seg_off), _p(sel_anchor), _p(sel_score), _p(sel_box), _p(sel_su),
-                      _p(sel_dir), _p(sel_rank))
+                      _p(sel_dir), _p(sel_rank), _p(nms_boxes), _p(nms_order), C.c_int(force_scalar))
+    for s in range(S):          # what pf_nms's sort would have produced: the boxes in order, the identity permutation
+        lo, n = seg_off[s], sel_num[s]
+        assert np.array_equal(nms_order[s * pre_max: s * pre_max + n], np.arange(n))
+        assert np.array_equal(nms_boxes[s * pre_max: s * pre_max + n].view(np.uint32), sel_su[lo:lo + n].view(np.uint32))
     keep = np.full((S, post_max), -1, np.int32)
     keep_num = np.zeros(S, np.int32)
     for s in range(S):
@@ -114,8 +120,10 @@ def test_emulated_kernels_match_oracle(emul, fmap, B, mean_logit, pre_max, post_
     anchors, ranges = synth.anchors_3d(geom, fmap)
     cls, box, dirp, mask = synth.post_preds(B, len(anchors), seed, mean_logit=mean_logit)
     limit = LIMIT if seed != 2 else [-10.0, -12.0, 0.5, 5.0, 2.2, 2.0]
-    got = run_emul(emul, cls, box, dirp, mask if with_mask else None, anchors, ranges, limit, 0.05, pre_max, post_max, 0.1)
-    check_against_oracle(got, cls, box, dirp, mask if with_mask else None, anchors, ranges, limit, 0.05, pre_max, post_max, 0.1)
+    for force_scalar in (0, 1):     # the vectorised and the generic score kernel
+        got = run_emul(emul, cls, box, dirp, mask if with_mask else None, anchors, ranges, limit, 0.05, pre_max, post_max, 0.1,
+                       force_scalar)
+        check_against_oracle(got, cls, box, dirp, mask if with_mask else None, anchors, ranges, limit, 0.05, pre_max, post_max, 0.1)
 
 
 def test_emulated_select_with_ties_and_specials(emul):
@@ -139,3 +147,18 @@ def test_emulated_select_with_ties_and_specials(emul):
     check_against_oracle(got, cls, box, dirp, mask, anchors, ranges, LIMIT, 0.05, 40, 10, 0.1)
     first = got["sel_anchor"][:got["sel_num"][0]].tolist()
     assert first[0] == 7 and 5 not in first and 6 not in first and 8 not in first      # +inf first; NaN and -inf never
+
+
+def test_emulated_score_mask_around_the_threshold(emul):
+    """Logits within 0.01 of the threshold's logit: inside +-2e-3 the kernel evaluates the sigmoid, outside it decides by
+    comparison; both must give the oracle's score mask (logits within 2e-7 of a tie in the score are excluded by the
+    generator)."""
+    cfg = util.cfgmod.builtin_config("20cm")
+    geom = util.cfgmod.derive_grid(cfg)
+    anchors, ranges = synth.anchors_3d(geom, (12, 12))
+    cls, box, dirp, mask = synth.post_preds(1, len(anchors), 11)
+    synth.post_threshold_band(cls, 0.05, 0.01, seed=12)
+    for force_scalar in (0, 1):
+        got = run_emul(emul, cls, box, dirp, mask, anchors, ranges, LIMIT, 0.05, 1000, 300, 0.1, force_scalar)
+        check_against_oracle(got, cls, box, dirp, mask, anchors, ranges, LIMIT, 0.05, 1000, 300, 0.1)
+    assert 0.3 < got["cand_count"].sum() / mask.sum() < 0.7
