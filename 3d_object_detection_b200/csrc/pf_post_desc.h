@@ -11,6 +11,7 @@ constexpr int kMaxClasses = 8;
 constexpr int kScoreThreads = 256;
 constexpr int kScorePerThread = 4;
 constexpr int kSelectThreads = 1024;
+constexpr int kSelectBatch = 8;       // key loads a thread of k_post_select keeps in flight
 constexpr int kDecodeThreads = 128;
 constexpr int kFinishThreads = 1024;   // >= post_max
 

@@ -168,7 +168,8 @@ k_post_score(Desc d, const float *__restrict__ cls, const uint8_t *__restrict__ 
 // key T, then the keys >= T (exactly pre_max of them: keys are unique) are collected.  A pass ends the search as soon as
 // the boundary bin is needed whole (typically once the bits that tell the logits apart are consumed: 3-4 passes).  The
 // upper bits of the keys are nearly constant, so a plain shared-memory histogram would serialise on one bin: each thread
-// counts runs of equal digits in registers and issues one atomic per run.  Bitonic sort in shared memory.
+// counts runs of equal digits in registers and issues one atomic per run.  One CTA reads its segment's keys through one SM,
+// so every sweep keeps kSelectBatch independent 8-byte loads per thread in flight.  Bitonic sort in shared memory.
 // dynamic shared memory: npad * 8 bytes, npad = pre_max rounded up to a power of two.
 __global__ void __launch_bounds__(kSelectThreads)
 k_post_select(Desc d, long long A, const unsigned long long *__restrict__ cand, const int *__restrict__ cand_count,
@@ -196,15 +197,23 @@ k_post_select(Desc d, long long A, const unsigned long long *__restrict__ cand, 
             const unsigned long long prefix = s_prefix;
             int run_d = -1;
             unsigned int run_n = 0;
-#pragma unroll 4
-            for (int i = tid; i < M; i += kSelectThreads) {
-                const unsigned long long key = src[i];
-                if (pass == 0 || (key >> (shift + 8)) == prefix) {
-                    const int dg = (int)((key >> shift) & 255ull);
-                    if (dg == run_d) ++run_n;
-                    else {
-                        if (run_n) atomicAdd(&s_hist[run_d], run_n);
-                        run_d = dg, run_n = 1;
+            for (int i0 = tid; i0 < M; i0 += kSelectThreads * kSelectBatch) {
+                unsigned long long kb[kSelectBatch];          // all loads of a batch in flight before the first use
+#pragma unroll
+                for (int u = 0; u < kSelectBatch; ++u) {
+                    const int i = i0 + u * kSelectThreads;
+                    kb[u] = i < M ? src[i] : 0ull;
+                }
+#pragma unroll
+                for (int u = 0; u < kSelectBatch; ++u) {
+                    const unsigned long long key = kb[u];
+                    if (i0 + u * kSelectThreads < M && (pass == 0 || (key >> (shift + 8)) == prefix)) {
+                        const int dg = (int)((key >> shift) & 255ull);
+                        if (dg == run_d) ++run_n;
+                        else {
+                            if (run_n) atomicAdd(&s_hist[run_d], run_n);
+                            run_d = dg, run_n = 1;
+                        }
                     }
                 }
             }
@@ -236,13 +245,19 @@ k_post_select(Desc d, long long A, const unsigned long long *__restrict__ cand, 
     if (tid == 0) s_n = 0;
     for (int i = tid; i < npad; i += kSelectThreads) s_keys[i] = 0;
     __syncthreads();
-#pragma unroll 4
-    for (int i = tid; i < M; i += kSelectThreads) {
-        const unsigned long long key = src[i];
-        if (key >= T) {
-            const int pos = atomicAdd(&s_n, 1);
-            if (pos < npad) s_keys[pos] = key;
+    for (int i0 = tid; i0 < M; i0 += kSelectThreads * kSelectBatch) {
+        unsigned long long kb[kSelectBatch];
+#pragma unroll
+        for (int u = 0; u < kSelectBatch; ++u) {
+            const int i = i0 + u * kSelectThreads;
+            kb[u] = i < M ? src[i] : 0ull;
         }
+#pragma unroll
+        for (int u = 0; u < kSelectBatch; ++u)
+            if (i0 + u * kSelectThreads < M && kb[u] >= T) {
+                const int pos = atomicAdd(&s_n, 1);
+                if (pos < npad) s_keys[pos] = kb[u];
+            }
     }
     __syncthreads();
     for (int kk = 2; kk <= npad; kk <<= 1)
