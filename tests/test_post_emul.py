@@ -113,6 +113,7 @@ def check_against_oracle(got, cls, box, dirp, mask, anchors, ranges, limit, thr,
     ((16, 16), 2, 0.0, 64, 64, False, 3),        # no anchor mask
     ((20, 20), 1, -1.0, 1000, 300, True, 4),     # the vehicle class holds ~1400 candidates: select 1000 of them
     ((6, 5), 1, -9.0, 1000, 300, True, 5),       # hardly any candidate
+    ((24, 24), 1, 1.0, 2000, 700, True, 6),      # > 1024 kept boxes in the frame: the finish kernel walks two chunks
 ])
 def test_emulated_kernels_match_oracle(emul, fmap, B, mean_logit, pre_max, post_max, with_mask, seed):
     cfg = util.cfgmod.builtin_config("20cm")
@@ -124,6 +125,8 @@ def test_emulated_kernels_match_oracle(emul, fmap, B, mean_logit, pre_max, post_
         got = run_emul(emul, cls, box, dirp, mask if with_mask else None, anchors, ranges, limit, 0.05, pre_max, post_max, 0.1,
                        force_scalar)
         check_against_oracle(got, cls, box, dirp, mask if with_mask else None, anchors, ranges, limit, 0.05, pre_max, post_max, 0.1)
+        if seed == 6:
+            assert got["det_num"][0] > 1024
 
 
 def test_emulated_select_with_ties_and_specials(emul):
