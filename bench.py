@@ -188,6 +188,23 @@ def cpu_arm(cfg, geom, frames, pts_cat, offs, steps, warmup, budget_s):
                       f"one frame per thread on {threads} of {cores} host cores"}
 
 
+def cpu_post_arm(cfg, geom, reps=3):
+    """cpu_baseline leg of the post-processing side measurement: the numpy restatement of Inference.infer_gpu's per-class
+    loop (oracle.postprocess_frame) on ONE frame of the sparse population, one host core."""
+    from oracle import oracle          # bench.py's cpu_baseline leg may run the oracle
+    synth = importlib.import_module("3d_object_detection_b200.synth")
+    fmap = (int(geom.grid_size[0]) // 2, int(geom.grid_size[1]) // 2)
+    anchors, ranges = synth.anchors_3d(geom, fmap)
+    cls, box, dirp, mask = synth.post_preds(1, len(anchors), 7, mean_logit=-9.6)
+    lim = [float(x) for x in cfg.get("center_limit", [-80.0, -80.0, -10.0, 80.0, 80.0, 10.0])]
+    oracle.postprocess_frame(cls[0], box[0], dirp[0], mask[0], anchors, ranges, lim)
+    t0 = time.perf_counter()
+    for _ in range(reps):
+        n = len(oracle.postprocess_frame(cls[0], box[0], dirp[0], mask[0], anchors, ranges, lim)[0])
+    return {"ms_per_frame": 1e3 * (time.perf_counter() - t0) / reps, "cores": 1, "kind": "port", "detections": n,
+            "sample": f"{reps} runs of one frame, sparse population, numpy restatement of Inference.infer_gpu's per-class loop"}
+
+
 def run_reference(args, rank, world):
     """--impl reference: the reference's CPU implementation of the path (oracle port; the Python/numba reference
     cannot travel to the GPU box) on the host cores.  Rank 0 only."""
@@ -607,6 +624,11 @@ def main():
         tiled, pts_c, offs_c = tile_for_cpu(r["frames"], cores)
         c = cpu_arm(cfg, r["geom"], tiled, pts_c, offs_c, steps=50, warmup=1, budget_s=args.cpu_seconds)
         line["cpu_baseline"] = {k: c[k] for k in ("value", "unit", "cores", "kind", "sample", "frames_per_s", "host_cores")}
+        if isinstance(line.get("postprocess"), dict) and "sparse" in line["postprocess"]:
+            try:
+                line["postprocess"]["cpu_baseline"] = cpu_post_arm(cfg, r["geom"])
+            except Exception as exc:
+                line["postprocess"]["cpu_baseline"] = {"error": f"{type(exc).__name__}: {exc}"}
     print(json.dumps(line), flush=True)
 
 
