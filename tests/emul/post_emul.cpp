@@ -52,6 +52,18 @@ int emul_post_front(int n_classes, const int *ranges, int n_ch, int pre_max, flo
     return 0;
 }
 
+// k_post_select alone on caller-made candidate lists: one class, segment f owns cand[f * A, f * A + cand_count[f])
+int emul_post_select(int pre_max, int n_seg, long long A, const unsigned long long *cand, const int *cand_count,
+                     unsigned long long *sel_key, int *sel_num)
+{
+    const int range[2] = {0, (int)A};
+    const Desc d = make_desc(1, range, 1, pre_max, 1, 0.5f, nullptr);
+    int npad = 1;
+    while (npad < pre_max) npad <<= 1;
+    pf_emul_launch(dim3((unsigned)n_seg), kSelectThreads, (size_t)npad * 8, [=] { k_post_select(d, A, cand, cand_count, sel_key, sel_num); });
+    return 0;
+}
+
 int emul_post_finish(int n_classes, const int *ranges, int pre_max, int post_max, const double *limit, int n_frames,
                      const int *seg_offsets, const int *keep, const int *keep_num, const float *sel_box,
                      const float *sel_score, const int *sel_dir, const int *sel_anchor, float *det_box, float *det_score,

@@ -165,3 +165,43 @@ def test_emulated_score_mask_around_the_threshold(emul):
         got = run_emul(emul, cls, box, dirp, mask, anchors, ranges, LIMIT, 0.05, 1000, 300, 0.1, force_scalar)
         check_against_oracle(got, cls, box, dirp, mask, anchors, ranges, LIMIT, 0.05, 1000, 300, 0.1)
     assert 0.3 < got["cand_count"].sum() / mask.sum() < 0.7
+
+
+def _select(L, lists, pre_max):
+    A = max(max((len(x) for x in lists), default=1), 1)
+    S = len(lists)
+    cand = np.zeros(S * A, np.uint64)
+    cnt = np.zeros(S, np.int32)
+    for s_, x in enumerate(lists):
+        cand[s_ * A: s_ * A + len(x)] = x
+        cnt[s_] = len(x)
+    sel_key = np.zeros(S * pre_max, np.uint64)
+    sel_num = np.full(S, -7, np.int32)
+    L.emul_post_select(C.c_int(pre_max), C.c_int(S), C.c_longlong(A), _p(cand), _p(cnt), _p(sel_key), _p(sel_num))
+    return [sel_key[s_ * pre_max: s_ * pre_max + sel_num[s_]] for s_ in range(S)]
+
+
+def test_emulated_radix_select_on_adversarial_keys(emul):
+    """k_post_select alone against numpy's sort: keys that differ only in their lowest bits, only in their highest, a
+    boundary that falls inside a run of equal upper words (the search has to go through all eight digits), M = pre_max,
+    M = pre_max + 1, a single candidate, none, and random 64-bit keys.  Keys are unique, as the kernel's are."""
+    emul.emul_post_select.restype = C.c_int
+    rng = np.random.default_rng(3)
+    hi = np.uint64(0xBF8ABCDE) << np.uint64(32)
+    lists = [
+        hi | rng.permutation(5000).astype(np.uint64),                                         # one upper word, 5000 lower words
+        (rng.permutation(3000).astype(np.uint64) << np.uint64(40)) | np.uint64(7),            # spread over the top digits
+        np.concatenate([hi | np.arange(1, 700, dtype=np.uint64), (hi + (np.uint64(1) << np.uint64(32))) | np.arange(1, 50, dtype=np.uint64)]),
+        rng.permutation(300).astype(np.uint64) + np.uint64(1),                                 # M = pre_max
+        rng.permutation(301).astype(np.uint64) + np.uint64(1),                                 # M = pre_max + 1
+        np.array([12345], np.uint64),
+        np.zeros(0, np.uint64),
+        np.unique(rng.integers(1, 2 ** 63, 20000, dtype=np.uint64)),
+        (np.uint64(0xFFFFFFFF) << np.uint64(32)) | rng.permutation(2048).astype(np.uint64),   # all-ones upper word
+    ]
+    lists[7] = rng.permutation(lists[7])
+    for pre_max in (300, 1, 1000):
+        got = _select(emul, lists, pre_max)
+        for x, g in zip(lists, got):
+            want = np.sort(x)[::-1][:pre_max]
+            assert np.array_equal(g, want), (pre_max, len(x))
