@@ -123,10 +123,15 @@ class Inference:
 
     def __init__(self, config, anchor_assigner, max_frames=None):
         torch = _torch()
-        dev = config['device']
-        if isinstance(dev, str) and not dev.startswith("cuda"):
+        dev = config['device']                      # an index (configs/*.json), "cuda:0", or a torch.device (ros_node.py:37-38)
+        name = str(dev)
+        if isinstance(dev, int) or name.isdigit():
+            index = int(name)
+        elif name.startswith("cuda"):
+            index = int(name.split(":")[1]) if ":" in name else 0
+        else:
             raise _lib.PillarFrontError(f"config['device'] = {dev!r}: the post-processing has no CPU fallback")
-        self.device = torch.device(dev) if isinstance(dev, str) else torch.device("cuda", int(dev))
+        self.device = torch.device("cuda", index)
         self._anchors_np = np.ascontiguousarray(anchor_assigner.anchors, np.float32).reshape(-1, 7)
         self._nms_pre_max_size = 1000
         self._nms_post_max_size = 300
@@ -201,4 +206,5 @@ class Inference:
             annos.append(anno)
         return annos
 
-    infer_torch = infer_gpu
+    infer_torch = infer_gpu     # :140-256, the same loop with the decode in torch
+    infer = infer_gpu           # what ros_node.py:75 calls (the reference's class has no such method any more)

@@ -172,6 +172,10 @@ def test_postprocess_abi_validation_and_refusal(pf):
         assert (i._nms_pre_max_size, i._nms_post_max_size, i._nms_iou_threshold, i._nms_score_threshold) == (1000, 300, 0.1, 0.05)
         with pytest.raises(pf.PillarFrontError):
             i.infer_gpu({}, dict(cls_preds=torch.zeros(1, 150, 1), box_preds=torch.zeros(1, 150, 7), dir_preds=torch.zeros(1, 150, 2)))
+    for dev in (0, "0", "cuda:1", "cuda", torch.device("cuda:0")):     # what configs/*.json and ros_node.py pass
+        i = inf.Inference(dict(device=dev, center_limit=lim, detect_class=["vehicle", "pedestrian"]), A_())
+        assert i.device.type == "cuda" and i.device.index == (1 if dev == "cuda:1" else 0)
+    assert inf.Inference.infer is inf.Inference.infer_gpu and inf.Inference.infer_torch is inf.Inference.infer_gpu
     anno = inf.get_start_result_anno()
     assert set(anno) == {"name", "truncated", "occluded", "alpha", "bbox", "dimensions", "location", "rotation_y", "score"}
     assert anno["bbox"].shape == (0, 4) and anno["location"].shape == (0, 3)
