@@ -198,6 +198,12 @@ def test_product_never_imports_oracle():
     for path in (ROOT / "3d_object_detection_b200").rglob("*.py"):
         text = path.read_text()
         assert not re.search(r"^\s*(from|import)\s+oracle\b", text, re.M), path
+        # nor the host emulation of the post-processing kernels (tests/emul/): that is a checker, never a fallback
+        assert "emul" not in text and "PF_HOST_EMUL" not in text, path
+    build_py = (ROOT / "3d_object_detection_b200" / "build.py").read_text()
+    assert "PF_HOST_EMUL" not in build_py
+    for path in (ROOT / "3d_object_detection_b200" / "csrc").glob("*.cu"):
+        assert "PF_HOST_EMUL" not in path.read_text(), path      # only the shared kernel header knows the switch
 
 
 def test_shard_frames(pf):
