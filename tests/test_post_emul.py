@@ -205,3 +205,38 @@ def test_emulated_radix_select_on_adversarial_keys(emul):
         for x, g in zip(lists, got):
             want = np.sort(x)[::-1][:pre_max]
             assert np.array_equal(g, want), (pre_max, len(x))
+
+
+def test_emulated_kernels_fuzz(emul):
+    """Seeded random configurations (feature map, batch, candidate density, pre / post max, score threshold incl. the two
+    ends where the logit pre-filter is off, 1-3 class channels, reordered class ranges with unassigned anchors between
+    them, quantised logits with many exact ties): both score kernels, every stage against the oracle."""
+    cfg = util.cfgmod.builtin_config("20cm")
+    geom = util.cfgmod.derive_grid(cfg)
+    rng = np.random.default_rng(20261105)
+    for _ in range(8):
+        fmap = (int(rng.integers(2, 12)), int(rng.integers(2, 12)))
+        B = int(rng.integers(1, 3))
+        mean = float(rng.choice([-8.0, -5.0, -3.0, -1.0, 1.0, 4.0]))
+        pre_max = int(rng.choice([1, 2, 7, 33, 64, 100, 257, 1000, 1500]))
+        post_max = int(rng.choice([1, 3, 10, 64, 300, 1000]))
+        thr = float(rng.choice([0.05, 0.3, 0.5, 0.9, 1e-7, 0.9995]))
+        nch = int(rng.choice([1, 1, 2, 3]))
+        limit = LIMIT if rng.random() < 0.5 else [-10.0, -12.0, 0.5, 5.0, 2.2, 2.0]
+        anchors, ranges = synth.anchors_3d(geom, fmap)
+        if rng.random() < 0.3:
+            ranges = [ranges[2], [ranges[0][0], ranges[0][1] - 3], ranges[1]]
+        seed = int(rng.integers(1 << 30))
+        cls, box, dirp, mask = synth.post_preds(B, len(anchors), seed, mean_logit=mean)
+        if nch > 1:
+            cls = np.concatenate([cls] + [synth.post_preds(B, len(anchors), seed + k, mean_logit=mean)[0] for k in range(1, nch)], axis=2)
+        if rng.random() < 0.3:
+            cls = np.round(cls * 2) / 2
+        with np.errstate(over="ignore"):      # keep the scores off the threshold: glibc's and numpy's exp differ by an ulp
+            sc = 1.0 / (1.0 + np.exp(-cls.max(axis=2).astype(np.float64)))
+        cls[np.abs(sc - np.float64(np.float32(thr))) < 1e-6 * max(thr, 1e-7) + 1e-9] += 0.25
+        m = mask if rng.random() < 0.7 else None
+        cls = np.ascontiguousarray(cls)
+        for force_scalar in (0, 1):
+            got = run_emul(emul, cls, box, dirp, m, anchors, ranges, limit, thr, pre_max, post_max, 0.1, force_scalar)
+            check_against_oracle(got, cls, box, dirp, m, anchors, ranges, limit, thr, pre_max, post_max, 0.1)
