@@ -240,3 +240,18 @@ def test_emulated_kernels_fuzz(emul):
         for force_scalar in (0, 1):
             got = run_emul(emul, cls, box, dirp, m, anchors, ranges, limit, thr, pre_max, post_max, 0.1, force_scalar)
             check_against_oracle(got, cls, box, dirp, m, anchors, ranges, limit, thr, pre_max, post_max, 0.1)
+
+
+@pytest.mark.parametrize("name", ["small", "topk", "range", "empty_class"])
+def test_emulated_kernels_match_reference_golden(emul, name):
+    """The kernel bodies (host emulation) against the annotations of the reference's own Inference.infer_gpu."""
+    g = util.load_post(name)
+    ranges = g["class_ranges"].tolist()
+    pre_max, post_max = int(g["pre_max"]), int(g["post_max"])
+    got = run_emul(emul, g["cls_preds"], g["box_preds"], g["dir_preds"], g["anchors_mask"], g["anchors"], ranges,
+                   g["center_limit"].tolist(), 0.05, pre_max, post_max, 0.1)
+    n = int(got["det_num"][0])
+    assert [str(g["detect_class"][k]) for k in got["det_class"][0, :n]] == [str(x) for x in g["name"]]
+    want = np.concatenate([g["location"], g["dimensions"], g["rotation_y"].reshape(-1, 1)], 1).astype(np.float32)
+    util.assert_post_boxes_close(got["det_box"][0, :n], want, name)
+    assert np.allclose(got["det_score"][0, :n], g["score"], rtol=2e-6, atol=0)
