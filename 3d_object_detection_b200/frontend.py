@@ -118,7 +118,8 @@ class PillarFrontEnd:
 
     def step(self, points, frame_offsets, pillar_feats=None, pfn=None, n_frames=None, max_frame_points=None):
         """One pass of the hot path over one batch.  Exactly one of pillar_feats / pfn feeds the scatter."""
-        fused = pfn is not None and hasattr(pfn, "folded") and not getattr(pfn, "training", True) and self.F == 4
+        fused = (pfn is not None and hasattr(pfn, "folded") and self.F == 4 and
+                 (pfn.fusable() if hasattr(pfn, "fusable") else not getattr(pfn, "training", True)))
         if fused:   # PointNet in eval mode: decorate + conv + BN + ReLU + max inside the gather kernel
             return self.scatter(self.voxelize_pfn(points, frame_offsets, pfn.folded(), n_frames, max_frame_points),
                                 n_frames)

@@ -104,8 +104,10 @@ def pfn_fused(voxels, num_points, coors, vx, vy, x_offset, y_offset, weight, sca
 
 class PointNet(nn.Module):
     """Pillar feature net: CUDA decoration + the reference's learned ``pfn_layers``.  In eval mode with 4-float
-    points the whole forward (decorate, conv, folded BN, ReLU, max) is one fused CUDA kernel (pf_pfn); in training
-    mode (batch statistics, autograd through the conv) the PFN runs in torch on the CUDA-decorated features."""
+    points and no gradient wanted (``torch.no_grad()``, as every inference loop of the reference runs it, or frozen
+    parameters) the whole forward (decorate, conv, folded BN, ReLU, max) is one fused CUDA kernel (pf_pfn); in
+    training mode (batch statistics) or whenever autograd records the call, the PFN runs in torch on the
+    CUDA-decorated features, so eval-mode gradients match the reference's."""
 
     def __init__(self, num_input_features, voxel_size, offset):
         super().__init__()
@@ -135,8 +137,21 @@ class PointNet(nn.Module):
             self._fold_key = key
         return self._fold
 
+    def wants_grad(self, voxels=None) -> bool:
+        """True when autograd would record this forward: grad mode on and the voxels or a PFN parameter require grad.
+        The fused kernel has no backward, so it may only replace the torch tail when this is False (the reference
+        module is differentiable in eval mode too: frozen-BN fine-tuning, saliency maps)."""
+        if not torch.is_grad_enabled():
+            return False
+        if voxels is not None and voxels.requires_grad:
+            return True
+        return any(p.requires_grad for p in self.pfn_layers.parameters())
+
+    def fusable(self, voxels=None) -> bool:
+        return not self.training and not self.wants_grad(voxels)
+
     def forward(self, voxels, num_point_per_voxel, coors):
-        if (not self.training and voxels.is_cuda and voxels.dtype == torch.float32 and voxels.dim() == 3
+        if (self.fusable(voxels) and voxels.is_cuda and voxels.dtype == torch.float32 and voxels.dim() == 3
                 and voxels.shape[2] == 4 and self.pfn_layers[0].weight.is_cuda):
             w, sc, sh = self.folded()
             return pfn_fused(voxels, num_point_per_voxel, coors, self.vx, self.vy, self.x_offset, self.y_offset,

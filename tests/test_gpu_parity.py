@@ -50,13 +50,16 @@ def test_voxelize_full_size(pfm, gkey, kind):
     want = oracle.generate(geom, pts, cfg["max_voxels"], cfg["max_num_points"])
     assert vn == len(want[2])
     util.assert_vox_equal((v, c, n), want, f"{gkey}/{kind}")
-    if util.sha(pts) == h["points_sha"]:      # same synthetic bits as in the build container -> reference hashes
-        assert util.sha(v) == h["voxels_sha"] and util.sha(c) == h["coors_sha"] and util.sha(n) == h["num_sha"]
     # device in -> device out, same bits
     dv, dc, dn, _ = vg.generate(torch.from_numpy(pts).cuda())
     assert dv.is_cuda and np.array_equal(_np(dv).view(np.uint32), v.view(np.uint32))
     assert np.array_equal(_np(dc), c) and np.array_equal(_np(dn), n)
     vg.close()
+    # the pin to the REFERENCE's own outputs at full size: loud when it cannot be applied (never a silent pass)
+    if util.sha(pts) != h["points_sha"]:
+        pytest.xfail(f"{gkey}/{kind}: the synthetic frame is not bit-identical on this host (numpy / libm differ from the "
+                     "build container), so the committed reference hashes do not apply; oracle parity above still held")
+    assert util.sha(v) == h["voxels_sha"] and util.sha(c) == h["coors_sha"] and util.sha(n) == h["num_sha"]
 
 
 def test_voxelize_feature_counts_and_strides(pfm):

@@ -76,6 +76,19 @@ def test_scatter_batched_and_backward(pf):
                               oracle.scatter(fe3, co3, nx3, ny3))
 
 
+@pytest.mark.parametrize("case", ["nuscene_s1", "20cm_s4_edges", "20cm_dup"])
+def test_scatter_backward_matches_reference_golden(pf, case):
+    """Row A7 pinned: pf_scatter_backward through autograd against the gradient the REFERENCE's own
+    PointPillarsScatter returned for the same coordinates and grad_canvas (oracle/make_golden_backward.py)."""
+    z, gc, coors = util.load_backward(case)
+    grid = z[case + "_grid"]
+    want = z[case + "_grad_feats"]
+    feats = torch.zeros((len(coors), 64), device="cuda").requires_grad_(True)
+    sc = pf.PointPillarsScatter(batch_size=1, output_shape=grid, num_input_features=64)
+    sc(feats, torch.from_numpy(coors).cuda()).backward(torch.from_numpy(gc).cuda())
+    assert np.array_equal(_np(feats.grad).view(np.uint32), want.view(np.uint32))
+
+
 @pytest.mark.parametrize("gkey,compact", [("20cm", False), ("20cm", True), ("nuscene", False), ("10cm", True)])
 def test_pipeline_batched(pf, gkey, compact):
     """voxelise -> decorate -> scatter for a ragged batch in one launch sequence, slab and collated layouts,
@@ -189,6 +202,30 @@ def test_fused_pfn_matches_reference_math(pf, gkey, name):
         np.abs(got - want).max()
     assert np.allclose(got, unfused, rtol=1e-4, atol=1e-4 * float(scale.max()))
     assert (got >= 0).all()
+
+
+def test_pointnet_eval_mode_is_differentiable(pf):
+    """under model.eval() with autograd on (frozen-BN fine-tuning, saliency) the module must stay
+    differentiable like the reference's; the fused kernel (no backward) may only run when no gradient is recorded."""
+    g = util.load_small("20cm", "s1")
+    cfg = util.small_config("20cm", g)
+    geom = cfgmod.derive_grid(cfg)
+    net = _random_pointnet(pf, cfg, geom, 9)                 # .eval()
+    v, n, c = (torch.from_numpy(g[k]).cuda() for k in ("voxels", "num", "coors"))
+    with torch.no_grad():
+        fused = net(v, n, c)
+    assert fused.grad_fn is None and not net.wants_grad(v)
+    out = net(v, n, c)                                       # grad mode on, parameters require grad -> torch tail
+    assert out.grad_fn is not None
+    assert torch.allclose(out, fused, rtol=1e-4, atol=1e-3)
+    w = net.pfn_layers[0].weight
+    (ga,) = torch.autograd.grad(out.square().sum(), w)
+    ref = net.features_to_pillars(net.decorate(v, n, c))
+    (gb,) = torch.autograd.grad(ref.square().sum(), w)
+    assert torch.equal(ga, gb)
+    for p in net.parameters():                               # frozen parameters: nothing to record -> fused again
+        p.requires_grad_(False)
+    assert net(v, n, c).grad_fn is None
 
 
 @pytest.mark.parametrize("gkey", ["20cm", "nuscene"])

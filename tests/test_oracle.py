@@ -88,6 +88,18 @@ def test_oracle_scatter_matches_reference(gkey, name):
     assert np.array_equal(gb, g["pillar_feats"])
 
 
+BACKWARD_CASES = ["nuscene_s1", "20cm_s4_edges", "20cm_dup"]
+
+
+@pytest.mark.parametrize("case", BACKWARD_CASES)
+def test_oracle_scatter_backward_matches_reference(case):
+    """Row A7: the oracle's gather against the gradient the REFERENCE's PointPillarsScatter returned through autograd
+    (oracle/make_golden_backward.py)."""
+    z, gc, coors = util.load_backward(case)
+    got = oracle.scatter_backward(gc, coors)
+    assert np.array_equal(got.view(np.uint32), z[case + "_grad_feats"].view(np.uint32))
+
+
 def test_micro_cases():
     """Hand-checkable cases of SURVEY.md §8c on the 20 cm grid."""
     cfg = cfgmod.builtin_config("20cm")
