@@ -17,7 +17,8 @@ _LAZY = {
     "merge_second_batch": "collate", "example_convert_to_torch": "collate",
     "nms_gpu": "nms", "nms": "nms", "nms_device": "nms",
     "Inference": "inference", "PostProcessor": "inference",
-    "PillarFrontEnd": "frontend", "shard_frames": "sharding", "PillarFrontError": "_lib",
+    "PillarFrontEnd": "frontend", "shard_frames": "sharding", "ShardedFrontEnd": "sharding", "place_devices": "sharding",
+    "PillarFrontError": "_lib",
 }
 
 __all__ = ["GRIDS", "CONFIG_GRID", "GridGeometry", "builtin_config", "derive_grid", "load_config", *_LAZY]

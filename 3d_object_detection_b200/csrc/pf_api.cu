@@ -2,8 +2,13 @@
 // Declarations and the reference functions each entry point replaces: include/pillarfront.h.
 #include <cstdarg>
 #include <cstdio>
+#include <cstring>
 #include <new>
 #include <string>
+
+#include <omp.h>
+
+#include <nvtx3/nvToolsExt.h>   // header-only; a no-op unless a profiler (nsys / ncu) is attached
 
 #include "pf_internal.cuh"
 
@@ -46,6 +51,12 @@ int cuda_fail(cudaError_t e, const char *what)
 inline size_t align_up(size_t x, size_t a) { return (x + a - 1) / a * a; }
 
 bool aligned16(const void *p) { return (reinterpret_cast<uintptr_t>(p) & 15) == 0; }
+
+// NVTX range around the enqueue of one C-ABI call (keep the path visible in traces)
+struct Range {
+    explicit Range(const char *name) { nvtxRangePushA(name); }
+    ~Range() { nvtxRangePop(); }
+};
 
 struct DeviceGuard {
     int prev = -1;
@@ -118,7 +129,7 @@ int pf_create(const pf_grid_desc *d, int max_frames, int max_points_per_frame, i
     size_t off = 0;
     auto carve = [&](size_t bytes) { size_t o = off; off = align_up(off + bytes, 256); return o; };
     const size_t o_grid = carve(B * p.cells * 4), o_cell = carve(B * p.npts_cap * 4), o_vr = carve(B * p.npts_cap * 4);
-    const size_t o_tc = carve(B * p.tiles_cap * 4), o_cnt = carve(B * p.tiles_cap * (size_t)p.vcols);
+    const size_t o_tc = carve(B * p.tiles_cap * 4), o_tk = carve(B * 4), o_cnt = carve(B * p.tiles_cap * (size_t)p.vcols);
     const size_t o_slot = carve(B * p.max_voxels * (size_t)p.P * 4), o_vcell = carve(B * p.max_voxels * 4);
     const size_t o_vcount = carve(B * p.max_voxels * 4), o_istar = carve(B * 4), o_vnum = carve(B * 4);
     const size_t o_map = carve(B * p.plane * 4);
@@ -131,6 +142,7 @@ int pf_create(const pf_grid_desc *d, int max_frames, int max_points_per_frame, i
     w.cellid = reinterpret_cast<int32_t *>(base + o_cell);
     w.vr = reinterpret_cast<int32_t *>(base + o_vr);
     w.tilecnt = reinterpret_cast<int32_t *>(base + o_tc);
+    w.ticket = reinterpret_cast<int32_t *>(base + o_tk);
     w.cnt = reinterpret_cast<uint8_t *>(base + o_cnt);
     w.slotidx = reinterpret_cast<int32_t *>(base + o_slot);
     w.vcell = reinterpret_cast<int32_t *>(base + o_vcell);
@@ -176,6 +188,35 @@ int pf_debug_stage_timing(pf_handle *h, int enable)
     return PF_OK;
 }
 
+int pf_stage_copy(void *dst, const void *src, size_t bytes, int threads)
+{
+    if (bytes == 0) return PF_OK;
+    if (!dst || !src) return fail(PF_ERR_INVALID_ARGUMENT, "pf_stage_copy: null pointer");
+    if (threads < 1) threads = 1;
+    if (threads > 16) threads = 16;
+    const size_t kMin = 256 * 1024;   // below this a second thread costs more than it saves
+    if (threads == 1 || bytes < 2 * kMin) {
+        memcpy(dst, src, bytes);
+        return PF_OK;
+    }
+    const size_t want = (bytes + kMin - 1) / kMin;
+    if ((size_t)threads > want) threads = (int)want;
+    const size_t chunk = ((bytes + threads - 1) / threads + 63) & ~(size_t)63;
+#pragma omp parallel for num_threads(threads) schedule(static, 1)
+    for (int t = 0; t < threads; ++t) {
+        const size_t lo = (size_t)t * chunk;
+        if (lo < bytes) memcpy(static_cast<char *>(dst) + lo, static_cast<const char *>(src) + lo, bytes - lo < chunk ? bytes - lo : chunk);
+    }
+    return PF_OK;
+}
+
+int pf_debug_set_fill_variant(int variant)
+{
+    if (variant < -1 || variant > 6) return fail(PF_ERR_INVALID_ARGUMENT, "pf_debug_set_fill_variant: variant %d outside -1..6", variant);
+    pf::set_fill_variant(variant);
+    return pf::fill_variant();
+}
+
 int pf_debug_stage_times(pf_handle *h, float *ms, int capacity)
 {
     if (!h || !ms) return fail(PF_ERR_INVALID_ARGUMENT, "pf_debug_stage_times: null argument");
@@ -211,6 +252,7 @@ static int voxelize_common(pf_handle *h, const pf::VoxelizeArgs &a, void *stream
         return fail(PF_ERR_STATE, "%s: the cell map kept by the previous call (%d frames) was not consumed: call "
                                   "pf_scatter_from_map or pf_discard_cell_map first", who, h->map_pending);
     DeviceGuard guard(h->device);
+    Range nvtx_range(who);
     cudaError_t e = pf::launch_voxelize(h->p, h->w, a, static_cast<cudaStream_t>(stream));
     if (e != cudaSuccess) return cuda_fail(e, who);
     h->map_pending = a.keep_cell_map ? a.n_frames : 0;
@@ -271,6 +313,7 @@ int pf_pfn(const float *voxels, const int32_t *num_points, const int32_t *coors,
     if (n_ch != 64 || num_features != 4) return fail(PF_ERR_UNSUPPORTED, "pf_pfn: needs n_ch == 64 and num_features == 4");
     if (coors_stride < 2 || max_points < 1 || max_points > 512) return fail(PF_ERR_UNSUPPORTED, "pf_pfn: coors_stride >= 2, 1 <= max_points <= 512");
     if (!aligned16(voxels) || !aligned16(pillar_feats)) return fail(PF_ERR_INVALID_ARGUMENT, "pf_pfn: voxels / pillar_feats must be 16-byte aligned");
+    Range nvtx_range("pf_pfn");
     cudaError_t e = pf::launch_decorate(voxels, num_points, coors, coors_stride, n_voxels, max_points, num_features, vx, vy,
                                         x_off, y_off, nullptr, static_cast<cudaStream_t>(stream), pfn_weight, pfn_scale,
                                         pfn_shift, pillar_feats);
@@ -288,6 +331,7 @@ int pf_decorate(const float *voxels, const int32_t *num_points, const int32_t *c
     if (max_points < 1 || max_points > 4096) return fail(PF_ERR_UNSUPPORTED, "pf_decorate: max_points %d outside 1..4096", max_points);
     if (num_features < 3 || num_features > 16) return fail(PF_ERR_UNSUPPORTED, "pf_decorate: num_features %d outside 3..16", num_features);
     if (!aligned16(features)) return fail(PF_ERR_INVALID_ARGUMENT, "pf_decorate: features must be 16-byte aligned");
+    Range nvtx_range("pf_decorate");
     cudaError_t e = pf::launch_decorate(voxels, num_points, coors, coors_stride, n_voxels, max_points, num_features, vx, vy,
                                         x_off, y_off, features, static_cast<cudaStream_t>(stream));
     return e == cudaSuccess ? PF_OK : cuda_fail(e, "pf_decorate");
@@ -303,6 +347,7 @@ int pf_scatter(pf_handle *h, const float *feats, int64_t feat_stride_v, int64_t 
     if (batch < 1 || batch > h->max_frames) return fail(PF_ERR_CAPACITY, "pf_scatter: batch %d outside [1, %d]", batch, h->max_frames);
     if (n_ch < 1) return fail(PF_ERR_INVALID_ARGUMENT, "pf_scatter: n_ch < 1");
     DeviceGuard guard(h->device);
+    Range nvtx_range("pf_scatter");
     cudaError_t e = pf::launch_scatter(h->p, h->w, feats, feat_stride_v, feat_stride_c, coors, coors_stride, n_voxels,
                                        batch, n_ch, canvas, static_cast<cudaStream_t>(stream));
     return e == cudaSuccess ? PF_OK : cuda_fail(e, "pf_scatter");
@@ -319,6 +364,7 @@ int pf_scatter_from_map(pf_handle *h, const float *feats, int64_t feat_stride_v,
     if (n_frames != h->map_pending)
         return fail(PF_ERR_INVALID_ARGUMENT, "pf_scatter_from_map: n_frames %d, but the kept map covers %d frames", n_frames, h->map_pending);
     DeviceGuard guard(h->device);
+    Range nvtx_range("pf_scatter_from_map");
     cudaError_t e = pf::launch_scatter_from_map(h->p, h->w, feats, feat_stride_v, feat_stride_c, n_frames, compact, n_ch,
                                                 canvas, static_cast<cudaStream_t>(stream));
     if (e != cudaSuccess) return cuda_fail(e, "pf_scatter_from_map");
@@ -345,6 +391,7 @@ int pf_scatter_backward(const float *grad_canvas, const int32_t *coors, int coor
     if (n_voxels == 0) return PF_OK;
     if (!grad_canvas || !coors || !grad_feats) return fail(PF_ERR_INVALID_ARGUMENT, "pf_scatter_backward: null argument");
     if (coors_stride < 2 || batch < 1 || n_ch < 1 || nx < 1 || ny < 1) return fail(PF_ERR_INVALID_ARGUMENT, "pf_scatter_backward: bad sizes");
+    Range nvtx_range("pf_scatter_backward");
     cudaError_t e = pf::launch_scatter_backward(grad_canvas, coors, coors_stride, n_voxels, batch, n_ch, nx, ny, grad_feats,
                                                 feat_stride_v, feat_stride_c, static_cast<cudaStream_t>(stream));
     return e == cudaSuccess ? PF_OK : cuda_fail(e, "pf_scatter_backward");
@@ -366,6 +413,7 @@ int pf_anchor_mask(const int32_t *coors, int coors_stride, const int32_t *voxel_
     if (rows_per_frame > 0 && !voxel_num) return fail(PF_ERR_INVALID_ARGUMENT, "pf_anchor_mask: the slab layout needs voxel_num");
     const bool frame_in_column = rows_per_frame == 0 && n_frames > 1;
     if (frame_in_column && coors_stride < 4) return fail(PF_ERR_INVALID_ARGUMENT, "pf_anchor_mask: frame id is column 3, coors_stride must be >= 4");
+    Range nvtx_range("pf_anchor_mask");
     cudaError_t e = pf::launch_anchor_mask(coors, coors_stride, voxel_num, n_rows, rows_per_frame, n_frames, nx, ny,
                                            anchor_coors, n_anchors, integral, mask, nullptr, static_cast<cudaStream_t>(stream));
     return e == cudaSuccess ? PF_OK : cuda_fail(e, "pf_anchor_mask");
@@ -390,6 +438,7 @@ int pf_nms(const float *boxes, const float *scores, const int32_t *seg_offsets, 
     if (!scratch || !keep || !keep_num) return fail(PF_ERR_INVALID_ARGUMENT, "pf_nms: null scratch/keep/keep_num");
     if (n_total > 0 && (!boxes || !scores)) return fail(PF_ERR_INVALID_ARGUMENT, "pf_nms: null boxes/scores");
     if (!aligned16(boxes) || (reinterpret_cast<uintptr_t>(scratch) & 255)) return fail(PF_ERR_INVALID_ARGUMENT, "pf_nms: boxes must be 16-byte and scratch 256-byte aligned");
+    Range nvtx_range("pf_nms");
     cudaError_t e = pf::launch_nms(boxes, scores, seg_offsets, n_segments, n_total, max_segment_boxes, iou_threshold, post_max,
                                    scratch, keep, keep_num, static_cast<cudaStream_t>(stream));
     return e == cudaSuccess ? PF_OK : cuda_fail(e, "pf_nms");
@@ -454,6 +503,7 @@ int pf_postprocess(const pf_post_desc *d, const float *cls_preds, const float *b
     k.score_thr = d->score_threshold;
     pf::post::set_prefilter(k);
     for (int i = 0; i < 6; ++i) k.limit[i] = d->center_limit[i];
+    Range nvtx_range("pf_postprocess");
     cudaError_t e = pf::launch_postprocess(k, d->iou_threshold, cls_preds, box_preds, dir_preds, anchors_mask, anchors, n_frames,
                                            n_anchors, scratch, det_boxes, det_scores, det_class, det_anchor, det_num,
                                            static_cast<cudaStream_t>(stream));

@@ -1,8 +1,13 @@
 // Internal declarations shared by the kernels and the C-ABI layer of libpillarfront.so (sm_100a only).
 #pragma once
 
-#include <cuda_runtime.h>
 #include <stdint.h>
+
+#ifdef PF_HOST_EMUL          // tests/emul: the same kernel bodies on host threads (test infrastructure, never the product)
+#include "warp_emul.h"
+#else
+#include <cuda_runtime.h>
+#endif
 
 #include "pillarfront.h"
 #include "pf_post_desc.h"
@@ -14,6 +19,7 @@ constexpr int kTileWarps = 8;        // warps per tile CTA in k_tile_rank
 constexpr int kTileSteps = 8;        // 32-point steps each warp owns, in point order
 constexpr int kTile = kTileWarps * kTileSteps * 32;   // 2048 points per tile
 constexpr int kCountCap = 255;       // saturation of the per-(tile,voxel) byte counters (>= max_points)
+constexpr int kQPer = 4;             // points per thread in the streaming point kernels (k_quantize, k_reset_cells)
 
 // Geometry and capacities, passed by value to every kernel.
 struct Params {
@@ -37,7 +43,8 @@ struct Work {
     int32_t *grid;      // [B][cells]   kEmpty | first point index (>=0) | ~voxel_id (<0)
     int32_t *cellid;    // [B][npts_cap] linear cell per point, -1 outside
     int32_t *vr;        // [B][npts_cap] (voxel_id << 8 | in-tile rank), -1 if dropped
-    int32_t *tilecnt;   // [B][tiles_cap] creators per tile
+    int32_t *tilecnt;   // [B][tiles_cap] look-back status words of k_assign: (state << 30 | creators), zeroed by k_quantize
+    int32_t *ticket;    // [B] next tile id to hand out (tiles are numbered in CTA start order), zeroed by k_quantize
     uint8_t *cnt;       // [B][tiles_cap][vcols] points per (tile, voxel), then its exclusive column scan
     int32_t *slotidx;   // [B][max_voxels][P] point index held by each voxel slot
     int32_t *vcell;     // [B][max_voxels] linear cell of each voxel
@@ -51,7 +58,9 @@ struct Work {
 // stage boundaries recorded when Work::ev is set (eager launches only; not capturable into a graph)
 enum Stage { kEvStart = 0, kEvQuantize, kEvAssign, kEvTileRank, kEvColumnScan, kEvSlot, kEvGather, kEvFillStart, kEvFill,
              kStageEvents };
+#ifndef PF_HOST_EMUL
 inline void mark(const Work &w, int k, cudaStream_t s) { if (w.ev) cudaEventRecord(w.ev[k], s); }
+#endif
 
 struct VoxelizeArgs {
     const float *points;
@@ -118,6 +127,9 @@ cudaError_t launch_anchor_mask(const int32_t *coors, int coors_stride, const int
                                long long n_anchors, int32_t *integral, uint8_t *mask, int *table_is_u16,
                                cudaStream_t stream);
 
+int fill_variant();            // pf_scatter.cu: which canvas-fill kernel runs (see pf_debug_set_fill_variant)
+void set_fill_variant(int v);
+
 size_t nms_scratch_bytes(int n_seg, int max_seg);
 cudaError_t launch_nms(const float *boxes, const float *scores, const int32_t *seg_offsets, int n_seg, long long n_total,
                        int max_seg, float thresh, int post_max, void *scratch, int32_t *keep, int32_t *keep_num,
@@ -133,7 +145,13 @@ cudaError_t launch_postprocess(const post::Desc &d, float iou_threshold, const f
                                int32_t *det_anchor, int32_t *det_num, cudaStream_t stream);
 
 // ---- small device helpers -------------------------------------------------------------------------------
-#ifdef __CUDACC__
+#if defined(__CUDACC__) || defined(PF_HOST_EMUL)
+
+#ifdef PF_HOST_EMUL
+#define PF_DYN_SHARED(T, name) T *name = reinterpret_cast<T *>(pf_emul_dyn_smem)
+#else
+#define PF_DYN_SHARED(T, name) extern __shared__ __align__(16) T name[]
+#endif
 
 // Linear cell of a point, or -1 if outside.  Bit-exact restatement of framework/voxel_generator.py:90-91:
 // fp32 subtract, IEEE fp32 divide, floor, and a range test that NaN / +-Inf / out-of-int32 values fail
@@ -158,6 +176,7 @@ __device__ __forceinline__ int div_small(int n, int d, unsigned m)
     return q;
 }
 
+#ifndef PF_HOST_EMUL
 __device__ __forceinline__ unsigned lanemask_lt()
 {
     unsigned m;
@@ -171,7 +190,12 @@ __device__ __forceinline__ void st_cs_f4(float *ptr, float a, float b, float c, 
     asm volatile("st.global.cs.v4.f32 [%0], {%1, %2, %3, %4};" ::"l"(ptr), "f"(a), "f"(b), "f"(c), "f"(d)
                  : "memory");
 }
+#endif
 
-#endif  // __CUDACC__
+// flag / status words other CTAs poll or publish (always through L2, never a cached copy)
+__device__ __forceinline__ int ld_flag(const int32_t *p) { return *reinterpret_cast<const volatile int32_t *>(p); }
+__device__ __forceinline__ void st_flag(int32_t *p, int v) { *reinterpret_cast<volatile int32_t *>(p) = v; }
+
+#endif  // __CUDACC__ || PF_HOST_EMUL
 
 }  // namespace pf

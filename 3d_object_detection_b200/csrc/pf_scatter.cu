@@ -6,9 +6,13 @@
 // write-once streaming pass: a warp owns 128 consecutive cells of one frame, reads the cell -> feature-row
 // map once (int4 per lane), and for every channel emits one fully coalesced 512-byte line of 16-byte
 // streaming stores, pulling feature values from L2 only for the occupied lanes.  HBM-write bound.
+#include <cstdlib>
+
 #include "pf_internal.cuh"
 
 namespace pf {
+
+constexpr int kFillDefault = 1;   // 32-byte stores: 242 vs 255 us at 20 cm x 8, 3.34 vs 3.59 ms at 10 cm x 32 (profiles/r2_fill_variants.md)
 
 // map[b][x*ny+y] = max(row) over pillars in that cell  (highest row wins == sequential index_put)
 __global__ void __launch_bounds__(256) k_map_index(const int32_t *__restrict__ coors, int coors_stride,
@@ -36,21 +40,32 @@ __global__ void __launch_bounds__(256) k_map_index(const int32_t *__restrict__ c
 constexpr int kFillWarps = 8;
 constexpr int kFillStage = 1152;   // floats of staging per warp: 17 occupied cells x 64 channels in one pass
 
-template <int MODE, bool FEAT4>
-__global__ void __launch_bounds__(kFillWarps * 32) k_canvas_fill(int32_t *__restrict__ map, const float *__restrict__ feats,
+// streaming (evict-first) 32-byte store, the widest the LSU has on sm_100 (SASS: STG.E.EF.256)
+__device__ __forceinline__ void st_cs_f8(float *ptr, const float (&v)[8])
+{
+    asm volatile("st.global.cs.v8.f32 [%0], {%1, %2, %3, %4, %5, %6, %7, %8};" ::"l"(ptr), "f"(v[0]), "f"(v[1]), "f"(v[2]),
+                 "f"(v[3]), "f"(v[4]), "f"(v[5]), "f"(v[6]), "f"(v[7])
+                 : "memory");
+}
+
+// CPL = cells per lane: 4 -> a warp owns 128 cells and stores 16 bytes per lane and channel (STG.128),
+//                       8 -> a warp owns 256 cells and stores 32 bytes per lane and channel (STG.256).
+template <int MODE, bool FEAT4, int CPL, int WARPS = kFillWarps, int STAGE = kFillStage>
+__global__ void __launch_bounds__(WARPS * 32) k_canvas_fill(int32_t *__restrict__ map, const float *__restrict__ feats,
                                                                  long long sv, long long sc,
                                                                  const int32_t *__restrict__ vnum, int max_voxels,
                                                                  int compact, int batch, int n_ch, int plane,
                                                                  float *__restrict__ canvas)
 {
-    __shared__ float s_stage[kFillWarps][kFillStage];
-    __shared__ int s_rows[kFillWarps][128];
+    constexpr int WCELLS = 32 * CPL;
+    __shared__ float s_stage[WARPS][STAGE];
+    __shared__ int s_rows[WARPS][WCELLS];
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
-    const int chunks = (plane + 127) >> 7;
-    const long long wg = (long long)blockIdx.x * kFillWarps + warp;
+    const int chunks = (plane + WCELLS - 1) / WCELLS;
+    const long long wg = (long long)blockIdx.x * WARPS + warp;
     if (wg >= (long long)chunks * batch) return;
     const int b = (int)(wg / chunks);
-    const int cell0 = (int)(wg % chunks) * 128 + lane * 4;
+    const int cell0 = (int)(wg % chunks) * WCELLS + lane * CPL;
     long long base = (long long)b * max_voxels;
     if (MODE == 1 && compact) {   // warp-uniform: row base of frame b = voxels of the frames before it
         int s = 0;
@@ -58,25 +73,38 @@ __global__ void __launch_bounds__(kFillWarps * 32) k_canvas_fill(int32_t *__rest
         for (int o = 16; o > 0; o >>= 1) s += __shfl_xor_sync(0xffffffffu, s, o);
         base = s;
     }
-    const bool in_plane = cell0 < plane;   // plane % 4 == 0 is guaranteed by the launcher
-    int row[4] = {-1, -1, -1, -1};
+    const bool in_plane = cell0 < plane;   // plane % CPL == 0 is guaranteed by the launcher
+    int row[CPL];
+#pragma unroll
+    for (int k = 0; k < CPL; ++k) row[k] = -1;
     if (in_plane) {
         int32_t *mp = map + (size_t)b * plane + cell0;
-        const int4 m = *reinterpret_cast<const int4 *>(mp);
-        if (MODE == 0) {
-            row[0] = m.x, row[1] = m.y, row[2] = m.z, row[3] = m.w;
-            if ((m.x & m.y & m.z & m.w) != -1) *reinterpret_cast<int4 *>(mp) = make_int4(-1, -1, -1, -1);
-        } else {
-            row[0] = m.x < 0 ? (int)(base + ~m.x) : -1;
-            row[1] = m.y < 0 ? (int)(base + ~m.y) : -1;
-            row[2] = m.z < 0 ? (int)(base + ~m.z) : -1;
-            row[3] = m.w < 0 ? (int)(base + ~m.w) : -1;
-            if (m.x != kEmpty || m.y != kEmpty || m.z != kEmpty || m.w != kEmpty)
-                *reinterpret_cast<int4 *>(mp) = make_int4(kEmpty, kEmpty, kEmpty, kEmpty);
+        bool dirty = false;
+#pragma unroll
+        for (int h = 0; h < CPL / 4; ++h) {
+            const int4 m = reinterpret_cast<const int4 *>(mp)[h];
+            const int mm[4] = {m.x, m.y, m.z, m.w};
+#pragma unroll
+            for (int k = 0; k < 4; ++k) {
+                if (MODE == 0) {
+                    row[4 * h + k] = mm[k];
+                    dirty |= mm[k] != -1;
+                } else {
+                    row[4 * h + k] = mm[k] < 0 ? (int)(base + ~mm[k]) : -1;
+                    dirty |= mm[k] != kEmpty;
+                }
+            }
+        }
+        if (dirty) {
+            const int e = MODE == 0 ? -1 : kEmpty;
+#pragma unroll
+            for (int h = 0; h < CPL / 4; ++h) reinterpret_cast<int4 *>(mp)[h] = make_int4(e, e, e, e);
         }
     }
     // slots: occupied cells of the warp, numbered in cell order
-    const int mine = (row[0] >= 0) + (row[1] >= 0) + (row[2] >= 0) + (row[3] >= 0);
+    int mine = 0;
+#pragma unroll
+    for (int k = 0; k < CPL; ++k) mine += row[k] >= 0;
     int incl = mine;
     for (int o = 1; o < 32; o <<= 1) {
         const int v = __shfl_up_sync(0xffffffffu, incl, o);
@@ -86,25 +114,33 @@ __global__ void __launch_bounds__(kFillWarps * 32) k_canvas_fill(int32_t *__rest
     float *dst = canvas + (size_t)b * n_ch * plane + cell0;
     if (n_occ == 0) {
         if (in_plane) {
+            const float z8[8] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
 #pragma unroll 8
-            for (int c = 0; c < n_ch; ++c) st_cs_f4(dst + (size_t)c * plane, 0.f, 0.f, 0.f, 0.f);
+            for (int c = 0; c < n_ch; ++c) {
+                if (CPL == 4) st_cs_f4(dst + (size_t)c * plane, 0.f, 0.f, 0.f, 0.f);
+                else {
+#pragma unroll
+                    for (int h = 0; h < CPL / 8; ++h) st_cs_f8(dst + (size_t)c * plane + 8 * h, z8);
+                }
+            }
         }
         return;
     }
-    int slot[4];
+    int slot[CPL];
     {
         int s = incl - mine;
 #pragma unroll
-        for (int k = 0; k < 4; ++k) {
+        for (int k = 0; k < CPL; ++k) {
             slot[k] = row[k] >= 0 ? s : -1;
             if (row[k] >= 0) s_rows[warp][s++] = row[k];
         }
     }
     __syncwarp();
     float *stage = s_stage[warp];
-    int cpp = ((kFillStage / n_occ) - 1) & ~3;   // channels per pass; row stride cpp+1 keeps reads conflict-free
-    if (cpp > n_ch) cpp = n_ch;
-    const int stride = cpp + 1;
+    int cpp = ((STAGE / n_occ) - 1) & ~3;   // channels per pass; row stride cpp+1 keeps reads conflict-free
+    int stride = cpp + 1;
+    if (cpp < 4) cpp = 4, stride = 4;            // only CPL = 8 with > 230 of 256 cells occupied: tight staging, conflicts accepted
+    if (cpp > n_ch) cpp = n_ch, stride = n_ch + 1;
     for (int c0 = 0; c0 < n_ch; c0 += cpp) {
         const int nc = (n_ch - c0) < cpp ? (n_ch - c0) : cpp;
         if (FEAT4) {
@@ -123,21 +159,176 @@ __global__ void __launch_bounds__(kFillWarps * 32) k_canvas_fill(int32_t *__rest
         }
         __syncwarp();
         if (in_plane) {
-            const float *p0 = stage + (slot[0] >= 0 ? slot[0] : 0) * stride;
-            const float *p1 = stage + (slot[1] >= 0 ? slot[1] : 0) * stride;
-            const float *p2 = stage + (slot[2] >= 0 ? slot[2] : 0) * stride;
-            const float *p3 = stage + (slot[3] >= 0 ? slot[3] : 0) * stride;
+            const float *ps[CPL];
+#pragma unroll
+            for (int k = 0; k < CPL; ++k) ps[k] = stage + (slot[k] >= 0 ? slot[k] : 0) * stride;
 #pragma unroll 4
             for (int cc = 0; cc < nc; ++cc) {
-                const float a0 = slot[0] >= 0 ? p0[cc] : 0.f;
-                const float a1 = slot[1] >= 0 ? p1[cc] : 0.f;
-                const float a2 = slot[2] >= 0 ? p2[cc] : 0.f;
-                const float a3 = slot[3] >= 0 ? p3[cc] : 0.f;
-                st_cs_f4(dst + (size_t)(c0 + cc) * plane, a0, a1, a2, a3);
+                float a[CPL < 8 ? 8 : CPL];
+#pragma unroll
+                for (int k = 0; k < CPL; ++k) a[k] = slot[k] >= 0 ? ps[k][cc] : 0.f;
+                if (CPL == 4) st_cs_f4(dst + (size_t)(c0 + cc) * plane, a[0], a[1], a[2], a[3]);
+                else {
+#pragma unroll
+                    for (int h = 0; h < CPL / 8; ++h) {
+                        const float (&a8)[8] = *reinterpret_cast<const float (*)[8]>(a + 8 * h);
+                        st_cs_f8(dst + (size_t)(c0 + cc) * plane + 8 * h, a8);
+                    }
+                }
             }
         }
         __syncwarp();
     }
+}
+
+// ---------------------------------------------------------------------------------------------------------
+// TMA variants (Blackwell-native store path): the canvas leaves the SM as bulk asynchronous copies
+// (cp.async.bulk.global.shared::cta, SASS UBLKCP.G.S) of whole channel lines instead of LSU stores.
+//
+// A CTA of 128 threads walks kTmaChunks consecutive chunks of CELLS cells with two [CT][CELLS (+4 pad)] fp32 tiles in
+// shared memory; an "item" is one chunk x one group of CT channels.  A tile is zeroed ONCE; per item only the occupied
+// columns are patched with the pillar rows, the tile goes out as CT bulk copies of CELLS * 4 bytes (issued by the lanes
+// of warp 0, one bulk group per lane and item), and the columns are zeroed again when the buffer comes round.  The map
+// read + feature fetch of item k+1 overlap the drain of item k; no store instruction touches the LSU.
+//   <128, 64>: one item per chunk, 64 copies of 512 bytes  (first version; bound by the per-copy cost of the TMA unit)
+//   <512, 16>: four items per chunk, 16 copies of 2 KB each (a quarter of the copies per byte)
+constexpr int kTmaThreads = 128;
+#ifndef PF_TMA_CHUNKS
+#define PF_TMA_CHUNKS 8
+#endif
+
+__device__ __forceinline__ void bulk_store(float *gdst, const float *ssrc, unsigned bytes, unsigned long long policy, bool hint)
+{
+    const unsigned sa = (unsigned)__cvta_generic_to_shared(ssrc);
+    if (hint)
+        asm volatile("cp.async.bulk.global.shared::cta.bulk_group.L2::cache_hint [%0], [%1], %2, %3;" ::"l"(gdst), "r"(sa),
+                     "r"(bytes), "l"(policy)
+                     : "memory");
+    else
+        asm volatile("cp.async.bulk.global.shared::cta.bulk_group [%0], [%1], %2;" ::"l"(gdst), "r"(sa), "r"(bytes) : "memory");
+}
+
+template <int MODE, bool HINT, int CELLS, int CT>
+__global__ void __launch_bounds__(kTmaThreads) k_canvas_fill_tma(int32_t *__restrict__ map, const float *__restrict__ feats,
+                                                                 long long sv, long long sc,
+                                                                 const int32_t *__restrict__ vnum, int max_voxels,
+                                                                 int compact, int batch, int n_ch, int plane,
+                                                                 int chunks_per_cta, float *__restrict__ canvas)
+{
+    constexpr int PITCH = CELLS + 4;    // floats per channel line in shared memory: 16-byte aligned rows, 4-way instead
+                                        // of 32-way bank conflicts when a column is patched
+    constexpr int CPT = CELLS / kTmaThreads;   // map entries per thread (1 or 4)
+    extern __shared__ __align__(128) float s_tile[];   // [2][CT][PITCH]
+    __shared__ int s_cell[CELLS], s_row[CELLS];        // occupied columns of the current chunk and their feature rows
+    __shared__ int s_pcell[2][CELLS];                  // columns currently patched into each tile
+    __shared__ int s_pn[2];
+    __shared__ int s_wcnt[kTmaThreads / 32];
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    const int chunks = (plane + CELLS - 1) / CELLS;
+    const long long total = (long long)chunks * batch;
+    const long long first = (long long)blockIdx.x * chunks_per_cta;
+    if (first >= total) return;
+    const int n_here = (int)((total - first) < chunks_per_cta ? (total - first) : chunks_per_cta);
+    const int groups = (n_ch + CT - 1) / CT;
+    constexpr int TILE = CT * PITCH;
+    for (int j = tid * 4; j < 2 * TILE; j += kTmaThreads * 4) *reinterpret_cast<float4 *>(s_tile + j) = make_float4(0.f, 0.f, 0.f, 0.f);
+    if (tid < 2) s_pn[tid] = 0;
+    unsigned long long policy = 0;
+    if (HINT) asm volatile("createpolicy.fractional.L2::evict_first.b64 %0, 1.0;" : "=l"(policy));
+    __syncthreads();
+
+    int item = 0;
+    for (int k = 0; k < n_here; ++k) {
+        const long long wg = first + k;
+        const int b = (int)(wg / chunks);
+        const int cell0 = (int)(wg % chunks) * CELLS;
+        const int ncell = (plane - cell0) < CELLS ? (plane - cell0) : CELLS;   // multiple of 4 (launcher)
+        // 1. map entries of my cells -> feature rows (and put the map back); compact the occupied ones
+        int row[CPT];
+        int mine = 0;
+        {
+            long long base = (long long)b * max_voxels;
+            if (MODE == 1 && compact) {
+                base = 0;
+                for (int q = 0; q < b; ++q) base += vnum[q];
+            }
+            int32_t *mp = map + (size_t)b * plane + cell0 + tid * CPT;
+            int m[CPT];
+#pragma unroll
+            for (int q = 0; q < CPT; ++q) m[q] = MODE == 0 ? -1 : kEmpty;
+            if (tid * CPT < ncell) {
+                if (CPT == 4) {
+                    const int4 v = *reinterpret_cast<const int4 *>(mp);
+                    m[0] = v.x, m[CPT > 1 ? 1 : 0] = v.y, m[CPT > 2 ? 2 : 0] = v.z, m[CPT > 3 ? 3 : 0] = v.w;
+                } else {
+                    m[0] = *mp;
+                }
+            }
+            bool dirty = false;
+#pragma unroll
+            for (int q = 0; q < CPT; ++q) {
+                if (MODE == 0) row[q] = m[q], dirty |= m[q] != -1;
+                else row[q] = m[q] < 0 ? (int)(base + ~m[q]) : -1, dirty |= m[q] != kEmpty;
+                mine += row[q] >= 0;
+            }
+            if (dirty) {
+                const int e = MODE == 0 ? -1 : kEmpty;
+                if (CPT == 4) *reinterpret_cast<int4 *>(mp) = make_int4(e, e, e, e);
+                else *mp = e;
+            }
+        }
+        int incl = mine;
+        for (int o = 1; o < 32; o <<= 1) {
+            const int v = __shfl_up_sync(0xffffffffu, incl, o);
+            if (lane >= o) incl += v;
+        }
+        __syncthreads();   // every thread is done with the previous chunk's lists
+        if (lane == 31) s_wcnt[warp] = incl;
+        __syncthreads();
+        int pos = incl - mine, n_occ = 0;
+#pragma unroll
+        for (int q = 0; q < kTmaThreads / 32; ++q) {
+            if (q < warp) pos += s_wcnt[q];
+            n_occ += s_wcnt[q];
+        }
+#pragma unroll
+        for (int q = 0; q < CPT; ++q)
+            if (row[q] >= 0) s_cell[pos] = tid * CPT + q, s_row[pos] = row[q], ++pos;
+        __syncthreads();
+
+        for (int g = 0; g < groups; ++g, ++item) {
+            const int buf = item & 1;
+            float *tile = s_tile + buf * TILE;
+            const int c0 = g * CT;
+            const int nc = (n_ch - c0) < CT ? (n_ch - c0) : CT;
+            // 2. the bulk copies that last read this tile (item - 2) must have finished reading shared memory
+            if (warp == 0 && item >= 2) asm volatile("cp.async.bulk.wait_group.read 1;" ::: "memory");
+            __syncthreads();
+            // 3. zero the columns patched last time, patch the new ones
+            const int n_old = s_pn[buf];
+            for (int e = tid; e < n_old * CT; e += kTmaThreads) {
+                const int s = e / CT, c = e - s * CT;
+                tile[c * PITCH + s_pcell[buf][s]] = 0.f;
+            }
+            __syncthreads();
+            for (int e = tid; e < n_occ; e += kTmaThreads) s_pcell[buf][e] = s_cell[e];
+            if (tid == 0) s_pn[buf] = n_occ;
+            for (int e = tid; e < n_occ * nc; e += kTmaThreads) {
+                const int s = e / nc, c = e - s * nc;
+                tile[c * PITCH + s_cell[s]] = __ldg(feats + (long long)s_row[s] * sv + (long long)(c0 + c) * sc);
+            }
+            // 4. generic-proxy writes -> visible to the async proxy, then the bulk copies of this item
+            asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+            __syncthreads();
+            if (warp == 0) {
+                float *dst = canvas + ((size_t)b * n_ch + c0) * plane + cell0;
+                for (int c = lane; c < nc; c += 32) bulk_store(dst + (size_t)c * plane, tile + c * PITCH, (unsigned)ncell * 4u, policy, HINT);
+                asm volatile("cp.async.bulk.commit_group;" ::: "memory");
+            }
+        }
+    }
+    if (warp == 0) asm volatile("cp.async.bulk.wait_group 0;" ::: "memory");   // shared memory must outlive the copies
+    __syncthreads();
 }
 
 // Fallback for planes that are not a multiple of 4 cells (no shipped config): one thread per canvas element.
@@ -192,6 +383,20 @@ __global__ void __launch_bounds__(256) k_scatter_backward(const float *__restric
     grad_feats[v * sv + c * sc] = g;
 }
 
+// fill variants (pf_debug_set_fill_variant / PF_FILL_VARIANT): 0 = warp, 16-byte stores (round 1's kernel), 1 = warp,
+// 32-byte stores, 2 / 3 = TMA bulk stores of 512 bytes (3: L2 evict-first hint), 4 / 5 = TMA bulk stores of 2 KB
+static int g_fill_variant = -1;
+
+int fill_variant()
+{
+    if (g_fill_variant < 0) {
+        const char *e = getenv("PF_FILL_VARIANT");
+        g_fill_variant = (e && e[0] >= '0' && e[0] <= '6') ? e[0] - '0' : kFillDefault;
+    }
+    return g_fill_variant;
+}
+void set_fill_variant(int v) { g_fill_variant = (v >= 0 && v <= 6) ? v : kFillDefault; }
+
 template <int MODE>
 static cudaError_t run_fill(int32_t *map, const float *feats, int64_t sv, int64_t sc, const int32_t *vnum,
                             int max_voxels, int compact, int batch, int n_ch, int plane, float *canvas,
@@ -207,15 +412,52 @@ static cudaError_t run_fill(int32_t *map, const float *feats, int64_t sv, int64_
         k_map_reset<<<148 * 4, 256, 0, stream>>>(map, (size_t)batch * plane, MODE == 0 ? -1 : kEmpty);
         return cudaGetLastError();
     }
-    const long long warps = (long long)((plane + 127) / 128) * batch;
-    const unsigned blocks = (unsigned)((warps + kFillWarps - 1) / kFillWarps);
+    const int variant = fill_variant();
     const bool feat4 = (sc == 1) && (sv % 4 == 0) && (n_ch % 4 == 0) && ((reinterpret_cast<uintptr_t>(feats) & 15) == 0);
-    if (feat4)
-        k_canvas_fill<MODE, true><<<blocks, kFillWarps * 32, 0, stream>>>(map, feats, sv, sc, vnum, max_voxels, compact, batch, n_ch,
-                                                              plane, canvas);
-    else
-        k_canvas_fill<MODE, false><<<blocks, kFillWarps * 32, 0, stream>>>(map, feats, sv, sc, vnum, max_voxels, compact, batch, n_ch,
-                                                               plane, canvas);
+    if (variant >= 2 && variant <= 5) {
+        // 2: 128-cell chunks x 64 channels (512-byte copies); 3: the same + L2 evict-first; 4: 512-cell chunks x 16 channels
+        // (2 KB copies); 5: 4 + evict-first
+        const bool big = variant >= 4;
+        const int cells = big ? 512 : 128, ct = big ? 16 : 64;
+        if (big || n_ch <= 64) {
+            const long long chunks = (long long)((plane + cells - 1) / cells) * batch;
+            const int per_cta = big ? (PF_TMA_CHUNKS / 4 > 0 ? PF_TMA_CHUNKS / 4 : 1) : PF_TMA_CHUNKS;
+            const unsigned blocks = (unsigned)((chunks + per_cta - 1) / per_cta);
+            const size_t smem = (size_t)2 * ct * (cells + 4) * sizeof(float);
+            void (*kern)(int32_t *, const float *, long long, long long, const int32_t *, int, int, int, int, int, int, float *);
+            switch (variant) {
+            case 2: kern = k_canvas_fill_tma<MODE, false, 128, 64>; break;
+            case 3: kern = k_canvas_fill_tma<MODE, true, 128, 64>; break;
+            case 4: kern = k_canvas_fill_tma<MODE, false, 512, 16>; break;
+            default: kern = k_canvas_fill_tma<MODE, true, 512, 16>; break;
+            }
+            cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+            if (e != cudaSuccess) return e;
+            kern<<<blocks, kTmaThreads, smem, stream>>>(map, feats, sv, sc, vnum, max_voxels, compact, batch, n_ch, plane, per_cta, canvas);
+            return cudaGetLastError();
+        }
+    }
+    const bool al32 = (reinterpret_cast<uintptr_t>(canvas) & 31) == 0;
+    if (variant == 6 && (plane % 16 == 0) && al32) {   // 512 cells per warp, 4 warps per CTA, two 32-byte stores per lane and channel
+        const long long warps6 = (long long)((plane + 511) / 512) * batch;
+        const unsigned blocks6 = (unsigned)((warps6 + 3) / 4);
+        if (feat4)
+            k_canvas_fill<MODE, true, 16, 4, 2304><<<blocks6, 128, 0, stream>>>(map, feats, sv, sc, vnum, max_voxels, compact, batch, n_ch, plane, canvas);
+        else
+            k_canvas_fill<MODE, false, 16, 4, 2304><<<blocks6, 128, 0, stream>>>(map, feats, sv, sc, vnum, max_voxels, compact, batch, n_ch, plane, canvas);
+        return cudaGetLastError();
+    }
+    const bool wide = variant == 1 && (plane % 8 == 0) && al32;
+    const int wcells = wide ? 256 : 128;
+    const long long warps = (long long)((plane + wcells - 1) / wcells) * batch;
+    const unsigned blocks = (unsigned)((warps + kFillWarps - 1) / kFillWarps);
+#define PF_FILL_LAUNCH(F4, CPL) k_canvas_fill<MODE, F4, CPL><<<blocks, kFillWarps * 32, 0, stream>>>(map, feats, sv, sc, vnum, max_voxels, compact, batch, n_ch, plane, canvas)
+    if (wide) {
+        if (feat4) PF_FILL_LAUNCH(true, 8); else PF_FILL_LAUNCH(false, 8);
+    } else {
+        if (feat4) PF_FILL_LAUNCH(true, 4); else PF_FILL_LAUNCH(false, 4);
+    }
+#undef PF_FILL_LAUNCH
     return cudaGetLastError();
 }
 

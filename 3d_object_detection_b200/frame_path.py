@@ -1,0 +1,71 @@
+"""Single-frame inference path as ONE CUDA graph: pinned staging -> H2D -> voxelise + decorate + fused PFN -> canvas
+fill -> D2H of the voxel count.  Used by ``VoxelGenerator.generate_and_scatter`` (the ``ros_node.py`` / ``train.py
+infer`` loop of the reference: one frame at a time, framework/dataset.py:213-229, ros_node.py:57-75)."""
+from __future__ import annotations
+
+import torch
+
+from . import _lib
+from .frontend import PillarFrontEnd
+
+
+class FusedFramePath:
+    def __init__(self, gen, cap: int, folded, n_channels: int = 64):
+        cfg = dict(detection_range=[float(x) for x in gen.detection_range], voxel_size=gen._voxel_size_cfg,
+                   max_voxels=gen.max_voxels, max_num_points=gen.max_num_points, num_point_features=4)
+        self.cap = cap
+        self.fe = PillarFrontEnd(cfg, max_batch=1, max_points_per_frame=cap, device=gen._device_index,
+                                 n_channels=n_channels, want_voxels=False, geometry=gen.geometry)
+        self.dev = self.fe.device
+        self.folded = folded
+        with torch.cuda.device(self.dev):
+            self.h_pts = torch.empty((cap, 4), dtype=torch.float32).pin_memory()
+            self.h_offs = torch.zeros((2,), dtype=torch.int32).pin_memory()
+            self.h_vnum = torch.zeros((1,), dtype=torch.int32).pin_memory()
+            self.np_pts, self.np_offs, self.np_vnum = self.h_pts.numpy(), self.h_offs.numpy(), self.h_vnum.numpy()
+            self.d_pts = torch.empty((cap, 4), dtype=torch.float32, device=self.dev)
+            self.d_offs = torch.zeros((2,), dtype=torch.int32, device=self.dev)
+            self.stream = torch.cuda.Stream(self.dev)
+            self.event = torch.cuda.Event()
+        self.graphs = {}
+
+    def _body(self, rows: int):
+        self.d_pts[:rows].copy_(self.h_pts[:rows], non_blocking=True)
+        self.d_offs.copy_(self.h_offs, non_blocking=True)
+        feats = self.fe.voxelize_pfn(self.d_pts, self.d_offs, self.folded, n_frames=1, max_frame_points=self.cap)
+        self.fe.scatter(feats, n_frames=1)
+        self.h_vnum.copy_(self.fe.voxel_num, non_blocking=True)
+
+    def _graph(self, rows: int):
+        g = self.graphs.get(rows)
+        if g is None:
+            with torch.cuda.device(self.dev), torch.cuda.stream(self.stream), torch.no_grad():
+                self._body(rows)
+                self.stream.synchronize()
+                g = torch.cuda.CUDAGraph()
+                with torch.cuda.graph(g, stream=self.stream):
+                    self._body(rows)
+            self.graphs[rows] = g
+        return g
+
+    def run(self, points, n: int, threads: int):
+        src = points if points.flags.c_contiguous else points.copy()
+        if n:
+            _lib.check(self.fe.handle.lib.pf_stage_copy(self.np_pts.ctypes.data, src.ctypes.data, src.nbytes, threads),
+                       "pf_stage_copy")
+        self.np_offs[1] = n
+        rows = min(self.cap, max(4096, (n + 4095) // 4096 * 4096))
+        g = self._graph(rows)
+        cur = torch.cuda.current_stream(self.dev)
+        self.stream.wait_stream(cur)                  # the consumer of the previous canvas may still be reading it
+        with torch.cuda.stream(self.stream):
+            g.replay()
+            self.event.record(self.stream)
+        cur.wait_event(self.event)
+        self.event.synchronize()
+        v = int(self.np_vnum[0])
+        return self.fe.canvas, self.fe.coors[:v], v
+
+    def close(self):
+        self.graphs.clear()
+        self.fe.close()

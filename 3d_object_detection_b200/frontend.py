@@ -28,16 +28,18 @@ class PillarFrontEnd:
 
     @staticmethod
     def n_kernels_voxelize(max_frame_points: int) -> int:
-        """Launches of one pf_voxelize_decorate call: quantize (two index ranges once a frame has >= 32768
-        points, csrc/pf_voxelize.cu), assign, tile_rank, column_scan, slot, gather(+decorate)."""
+        """Launches of one pf_voxelize_decorate call: quantize (two index ranges once a frame has >= 32768 points,
+        csrc/pf_voxelize.cu), assign, tile_rank, column_scan, slot, gather(+decorate)."""
         return (2 if max_frame_points >= 32 * 1024 else 1) + 5
 
     def __init__(self, config, max_batch, max_points_per_frame, device=0, n_channels=64, want_voxels=True,
-                 compact=False):
+                 compact=False, geometry=None):
         if not torch.cuda.is_available():
             raise _lib.PillarFrontError("no CUDA device: the pillar front end has no CPU fallback")
         cfg = dict(config)
-        self.geometry = derive_grid(cfg)
+        # `geometry`: an already derived grid (derive_grid snaps the range, so deriving twice from a snapped range is
+        # not guaranteed to be the identity in fp32)
+        self.geometry = geometry if geometry is not None else derive_grid(cfg)
         g = self.geometry
         self.device = torch.device("cuda", int(device))
         self.B = int(max_batch)

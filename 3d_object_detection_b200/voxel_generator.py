@@ -5,14 +5,29 @@ the same return values as ``VoxelGenerator.generate`` (framework/voxel_generator
 ``(V, P, F)`` fp32, ``coors`` ``(V, 3)`` int32 in **x, y, z** order (F3) and ``num_points_per_voxel`` ``(V,)``
 int32, bit-identical to the numba loop including its ``max_voxels`` early ``break`` (F5).
 
+The single-frame path is the reference's real operating point (every ``configs/*.json`` has ``batch_size: 1``;
+``InferData.get``, framework/dataset.py:213-229; ros_node.py:70-75), so ``generate`` is built for latency:
+
+* per instance and per ``(F, point-capacity bucket)`` one :class:`_FramePath` -- workspace handle, device buffers, a
+  PINNED input staging buffer, and ONE CUDA graph holding "H2D of the staged frame + frame length, the voxelise
+  kernels, D2H of the voxel count"; nothing is allocated, no ``torch.tensor(...)`` / ``.item()`` per call;
+* the numpy frame is copied into the staging buffer by ``pf_stage_copy`` (a few host threads), the graph is replayed,
+  the host waits on one event and reads ``V`` from pinned memory, then copies exactly ``V`` rows out;
+* numpy outputs land directly in a pinned block taken from a small recycling pool and are returned as views of it:
+  a block is only handed out again once every array that was returned from it has been released (the reference's
+  ownership contract -- callers may keep the arrays -- holds; nothing aliases a live result; an asynchronous copy a
+  caller starts FROM such an array must have completed before it drops the array, which is how
+  ``example_convert_to_torch``'s ``torch.as_tensor(..., device=)`` behaves);
+* ``device_outputs=True`` (or CUDA tensor input) returns fresh torch CUDA tensors of exactly ``V`` rows;
+* :meth:`VoxelGenerator.generate_and_scatter` goes one further for ``ros_node.py``-style loops: voxelise + decorate +
+  fused PFN + canvas fill as one graph, one synchronisation per frame.
+
 Differences, all deliberate (SURVEY.md §8b "Errors", "Threading"):
 
 * points must be float32 ``(N, F>=3)``; anything else raises ``TypeError`` / ``ValueError`` (the reference
   would JIT a float64 specialisation).
 * CUDA cannot be used from forked DataLoader workers: use ``num_workers = 0`` (what ntusl_20cm.json,
   ntusl_10cm.json and seven_20cm.json already set) or a ``spawn`` context.
-* ``generate(points, device_outputs=True)`` (or CUDA tensor input) returns torch CUDA tensors and skips the
-  device->host copy; ``example_convert_to_torch`` (framework/utils.py:7-20) passes them through unchanged.
 * ``generate_batch`` voxelises a list of frames in one launch sequence and returns the collated layout of
   ``merge_second_batch`` (framework/utils.py:23-48): concatenated rows, frame id in the LAST coors column.
 
@@ -20,15 +35,101 @@ There is no CPU fallback: without a CUDA device ``generate`` raises.
 """
 from __future__ import annotations
 
+import os
+import sys
+import time
+
 import numpy as np
 
 from . import _lib
 from .config import derive_grid
 
+_BUCKET = 32768          # point-capacity granularity of the single-frame graphs
+_POOL_MAX = 8            # pinned output blocks kept per instance before falling back to pageable copies
+
 
 def _torch():
     import torch
     return torch
+
+
+def _stage_threads() -> int:
+    try:
+        n = len(os.sched_getaffinity(0))
+    except Exception:
+        n = os.cpu_count() or 1
+    return max(1, min(4, n))
+
+
+class _OutBlock:
+    """One pinned host block for the numpy outputs of a frame; recycled once all views handed out from it died."""
+
+    def __init__(self, torch, mv, P, F):
+        self.tv = torch.empty((mv, P, F), dtype=torch.float32).pin_memory()
+        self.tc = torch.empty((mv, 3), dtype=torch.int32).pin_memory()
+        self.tn = torch.empty((mv,), dtype=torch.int32).pin_memory()
+        self.nv, self.nc, self.nn = self.tv.numpy(), self.tc.numpy(), self.tn.numpy()
+        self._base = tuple(sys.getrefcount(a) for a in (self.nv, self.nc, self.nn))
+
+    def free(self) -> bool:
+        return tuple(sys.getrefcount(a) for a in (self.nv, self.nc, self.nn)) == self._base
+
+
+class _FramePath:
+    """Everything one single-frame call needs for a fixed (F, capacity): buffers, staging, graph."""
+
+    def __init__(self, gen: "VoxelGenerator", n_feat: int, cap: int):
+        torch = _torch()
+        self.cap, self.F = cap, n_feat
+        dev = torch.device("cuda", gen._device_index)
+        self.dev = dev
+        mv, P = gen.max_voxels, gen.max_num_points
+        self.handle = _lib.Handle(gen.geometry, mv, P, n_feat, 1, cap, gen._device_index)
+        with torch.cuda.device(dev):
+            self.h_pts = torch.empty((cap, n_feat), dtype=torch.float32).pin_memory()
+            self.h_offs = torch.zeros((2,), dtype=torch.int32).pin_memory()
+            self.h_vnum = torch.zeros((1,), dtype=torch.int32).pin_memory()
+            self.np_pts, self.np_offs, self.np_vnum = self.h_pts.numpy(), self.h_offs.numpy(), self.h_vnum.numpy()
+            self.d_pts = torch.empty((cap, n_feat), dtype=torch.float32, device=dev)
+            self.d_offs = torch.zeros((2,), dtype=torch.int32, device=dev)
+            self.voxels = torch.empty((mv, P, n_feat), dtype=torch.float32, device=dev)
+            self.coors = torch.empty((mv, 3), dtype=torch.int32, device=dev)
+            self.num = torch.empty((mv,), dtype=torch.int32, device=dev)
+            self.vnum = torch.zeros((1,), dtype=torch.int32, device=dev)
+            self.event = torch.cuda.Event()
+            self.stream = torch.cuda.Stream(dev)      # copies + graph run here; callers' streams wait on `event`
+            self.graphs = {}                          # staged point rows (multiple of 4096) -> CUDAGraph
+            self.graph_cuda_in = None
+
+    def _body(self, src_host: bool, rows: int):
+        torch = _torch()
+        h = self.handle
+        if src_host:
+            self.d_pts[:rows].copy_(self.h_pts[:rows], non_blocking=True)
+            self.d_offs.copy_(self.h_offs, non_blocking=True)
+        stream = torch.cuda.current_stream(self.dev).cuda_stream
+        _lib.check(h.lib.pf_voxelize(h.ptr, self.d_pts.data_ptr(), self.d_offs.data_ptr(), 1, self.cap, self.F, 0, 3,
+                                     self.voxels.data_ptr(), self.coors.data_ptr(), self.num.data_ptr(),
+                                     self.vnum.data_ptr(), stream), "pf_voxelize")
+        self.h_vnum.copy_(self.vnum, non_blocking=True)
+
+    def graph_for(self, rows: int):
+        """The graph whose H2D node moves `rows` staged point rows (rows is a multiple of 4096 <= cap)."""
+        torch = _torch()
+        g = self.graphs.get(rows)
+        if g is None:
+            with torch.cuda.device(self.dev), torch.cuda.stream(self.stream):
+                self._body(True, rows)                # warm-up outside capture (first-use initialisation); idempotent
+                self.stream.synchronize()
+                g = torch.cuda.CUDAGraph()
+                with torch.cuda.graph(g, stream=self.stream):
+                    self._body(True, rows)
+            self.graphs[rows] = g
+        return g
+
+    def close(self):
+        self.graphs.clear()
+        self.handle.close()
 
 
 class VoxelGenerator:
@@ -44,6 +145,7 @@ class VoxelGenerator:
         self.max_num_points = int(config["max_num_points"])
         self.max_voxels = int(config["max_voxels"])
         self.num_point_features = int(config.get("num_point_features", 4))
+        self._voxel_size_cfg = list(config["voxel_size"])
         # the reference writes these four keys back; AnchorAssigner, the datasets and the networks read them
         # (framework/voxel_generator.py:23-26)
         config["detection_range"] = geom.detection_range
@@ -53,7 +155,12 @@ class VoxelGenerator:
         dev = device if device is not None else config.get("device", 0)
         self._device_index = self._parse_device(dev)
         self._cap_hint = int(max_points_per_frame) if max_points_per_frame else 0
-        self._handles = {}      # (max_frames, F) -> _lib.Handle
+        self._handles = {}      # F -> _lib.Handle of the batched / CUDA-input path
+        self._paths = {}        # (F, capacity) -> _FramePath of the single-frame path
+        self._pool = []         # _OutBlock
+        self._pool_F = None
+        self._fused = {}        # (F, capacity, id(pfn)) -> _FusedPath (generate_and_scatter)
+        self._threads = _stage_threads()
         self.voxel_time = 0.0   # kept for parity with InferData's timers (framework/dataset.py:208)
 
     # ------------------------------------------------------------------------------------------------
@@ -68,10 +175,13 @@ class VoxelGenerator:
             return int(s)
         raise ValueError(f"VoxelGenerator needs a CUDA device, got {dev!r} (no CPU fallback)")
 
+    def _require_cuda(self):
+        if not _torch().cuda.is_available():
+            raise _lib.PillarFrontError("no CUDA device: the pillar front end has no CPU fallback")
+
     def _handle(self, n_frames: int, n_feat: int, max_pts: int) -> "_lib.Handle":
         torch = _torch()
-        if not torch.cuda.is_available():
-            raise _lib.PillarFrontError("no CUDA device: the pillar front end has no CPU fallback")
+        self._require_cuda()
         key = n_feat
         h = self._handles.get(key)
         if h is None or h.max_frames < n_frames or h.max_points_per_frame < max_pts:
@@ -88,27 +198,103 @@ class VoxelGenerator:
             self._handles[key] = h
         return h
 
-    def _to_device(self, points):
-        """Validate one frame and return a contiguous fp32 CUDA tensor (N, F)."""
+    @staticmethod
+    def _check_points(points):
+        """Validate one frame; returns ("numpy" | "torch", N, F)."""
         torch = _torch()
-        if not torch.cuda.is_available():
-            raise _lib.PillarFrontError("no CUDA device: the pillar front end has no CPU fallback")
-        dev = torch.device("cuda", self._device_index)
         if isinstance(points, np.ndarray):
             if points.dtype != np.float32:
                 raise TypeError(f"points must be float32, got {points.dtype}")
             if points.ndim != 2 or points.shape[1] < 3:
                 raise ValueError(f"points must have shape (N, F>=3), got {points.shape}")
-            t = torch.from_numpy(np.ascontiguousarray(points))
-            return t.to(dev, non_blocking=True), False
-        if isinstance(points, torch.Tensor):
+            kind = "numpy"
+        elif isinstance(points, torch.Tensor):
             if points.dtype != torch.float32:
                 raise TypeError(f"points must be float32, got {points.dtype}")
             if points.dim() != 2 or points.shape[1] < 3:
                 raise ValueError(f"points must have shape (N, F>=3), got {tuple(points.shape)}")
-            on_dev = points.is_cuda
-            return points.contiguous().to(dev, non_blocking=True), on_dev
-        raise TypeError(f"points must be a numpy array or a torch tensor, got {type(points).__name__}")
+            kind = "torch"
+        else:
+            raise TypeError(f"points must be a numpy array or a torch tensor, got {type(points).__name__}")
+        n_feat = int(points.shape[1])
+        if not 3 <= n_feat <= 16:
+            raise ValueError(f"point features must be 3..16, got {n_feat}")
+        return kind, int(points.shape[0]), n_feat
+
+    def _to_device(self, points):
+        """Validate one frame and return a contiguous fp32 CUDA tensor (N, F) (batched / CUDA-input path)."""
+        torch = _torch()
+        self._require_cuda()
+        kind, _, _ = self._check_points(points)
+        dev = torch.device("cuda", self._device_index)
+        if kind == "numpy":
+            t = torch.from_numpy(np.ascontiguousarray(points))
+            return t.to(dev, non_blocking=True), False
+        return points.contiguous().to(dev, non_blocking=True), points.is_cuda
+
+    # ---- single-frame fast path ------------------------------------------------------------------------
+    def _capacity(self, n: int) -> int:
+        want = max(n, self._cap_hint, 1)
+        return (want + _BUCKET - 1) // _BUCKET * _BUCKET
+
+    def _path(self, n_feat: int, n: int) -> _FramePath:
+        self._require_cuda()
+        key = (n_feat, self._capacity(n))
+        p = self._paths.get(key)
+        if p is None:
+            p = _FramePath(self, n_feat, key[1])
+            self._paths[key] = p
+        return p
+
+    def _stage(self, path, points, n: int) -> int:
+        """Copy the frame into the path's pinned staging buffer; returns the rows the H2D node must move."""
+        src = points if points.flags.c_contiguous else np.ascontiguousarray(points)
+        if n:
+            _lib.check(path.handle.lib.pf_stage_copy(path.np_pts.ctypes.data, src.ctypes.data, src.nbytes, self._threads),
+                       "pf_stage_copy")
+        path.np_offs[1] = n
+        return min(path.cap, max(4096, (n + 4095) // 4096 * 4096))
+
+    def _out_block(self) -> "_OutBlock | None":
+        for b in self._pool:
+            if b.free():
+                return b
+        if len(self._pool) < _POOL_MAX:
+            b = _OutBlock(_torch(), self.max_voxels, self.max_num_points, self._pool_F)
+            self._pool.append(b)
+            return b
+        return None
+
+    def _generate_frame(self, points, n: int, n_feat: int, device_outputs: bool):
+        torch = _torch()
+        path = self._path(n_feat, n)
+        rows = self._stage(path, points, n)
+        g = path.graph_for(rows)
+        cur = torch.cuda.current_stream(path.dev)
+        with torch.cuda.stream(path.stream):
+            g.replay()
+            path.event.record(path.stream)
+        path.event.synchronize()                      # the only wait in front of the read-back: V is data dependent
+        v = int(path.np_vnum[0])
+        if device_outputs:
+            cur.wait_event(path.event)
+            with torch.cuda.device(path.dev):
+                out = (path.voxels[:v].clone(), path.coors[:v].clone(), path.num[:v].clone())
+            path.stream.wait_stream(cur)              # the next replay must not overwrite what the clones still read
+            return out, v
+        if self._pool and self._pool_F != n_feat:
+            self._pool = []
+        self._pool_F = n_feat
+        blk = self._out_block()
+        with torch.cuda.stream(path.stream):
+            if blk is not None:                       # D2H of exactly V rows, straight into the arrays handed out
+                blk.tv[:v].copy_(path.voxels[:v], non_blocking=True)
+                blk.tc[:v].copy_(path.coors[:v], non_blocking=True)
+                blk.tn[:v].copy_(path.num[:v], non_blocking=True)
+                path.stream.synchronize()
+                return (blk.nv[:v], blk.nc[:v], blk.nn[:v]), v
+            out = (path.voxels[:v].cpu().numpy(), path.coors[:v].cpu().numpy(), path.num[:v].cpu().numpy())
+        return out, v
 
     # ------------------------------------------------------------------------------------------------
     def _run(self, frames_dev, compact: bool, coors_stride: int):
@@ -141,16 +327,23 @@ class VoxelGenerator:
 
     def generate(self, points, device_outputs=None):
         """One frame -> (voxels, coors, num_points_per_voxel)[, voxel_num]; numpy in -> numpy out."""
-        import time
         t0 = time.time()
-        dev_pts, was_cuda = self._to_device(points)
+        self._require_cuda()
+        kind, n, n_feat = self._check_points(points)
+        on_dev = kind == "torch" and points.is_cuda
         if device_outputs is None:
-            device_outputs = was_cuda
-        voxels, coors, num, vnum = self._run([dev_pts], compact=False, coors_stride=3)
-        v = int(vnum.item())                       # the only synchronisation: V is data dependent
-        voxels, coors, num = voxels[:v], coors[:v], num[:v]
-        if not device_outputs:
-            voxels, coors, num = voxels.cpu().numpy(), coors.cpu().numpy(), num.cpu().numpy()
+            device_outputs = on_dev
+        if kind == "torch" and not on_dev:
+            points, kind = points.contiguous().numpy(), "numpy"
+        if kind == "numpy":
+            (voxels, coors, num), v = self._generate_frame(points, n, n_feat, bool(device_outputs))
+        else:                                          # CUDA tensor in: no staging, eager launch on the caller's stream
+            dv, dc, dn, vnum = self._run([points.contiguous().to(_torch().device("cuda", self._device_index))],
+                                         compact=False, coors_stride=3)
+            v = int(vnum.item())
+            voxels, coors, num = dv[:v], dc[:v], dn[:v]
+            if not device_outputs:
+                voxels, coors, num = voxels.cpu().numpy(), coors.cpu().numpy(), num.cpu().numpy()
         self.voxel_time += time.time() - t0
         if self._returns_voxel_num:
             return voxels, coors, num, v
@@ -171,10 +364,42 @@ class VoxelGenerator:
             out = {k: (v.cpu().numpy() if hasattr(v, "cpu") else v) for k, v in out.items()}
         return out
 
+    # ---- one graph per frame: voxelise + decorate + PFN + canvas --------------------------------------
+    def generate_and_scatter(self, points, pfn, n_channels=64):
+        """Single-frame fast path for inference loops (ros_node.py:57-75, train.py infer): numpy frame in, BEV canvas
+        ``(1, C, nx, ny)`` on the device out, as ONE CUDA graph (H2D, voxelise, decorate + fused PFN, canvas fill, D2H of
+        the voxel count) and one synchronisation.  ``pfn`` is a :class:`PointNet` in eval mode; its folded weights are
+        read when the graph is first captured (call again after changing them: the cache key follows their versions).
+        Returns ``(canvas, coors (V, 4) int32 CUDA, voxel_num)``; the tensors are views of per-instance buffers, valid
+        until the next call."""
+        from .frame_path import FusedFramePath
+        self._require_cuda()
+        kind, n, n_feat = self._check_points(points)
+        if kind != "numpy":
+            points = points.detach().cpu().contiguous().numpy()
+        if n_feat != 4:
+            raise ValueError("generate_and_scatter needs 4 floats per point (the fused PFN kernel)")
+        fold = pfn.folded()
+        key = (self._capacity(n), id(pfn), tuple(t.data_ptr() for t in fold), getattr(pfn, "_fold_key", None))
+        fp = self._fused.get(key)
+        if fp is None:
+            for old in [k for k in self._fused if k[0] == key[0] and k[1] == key[1]]:
+                self._fused.pop(old).close()
+            fp = FusedFramePath(self, key[0], fold, n_channels)
+            self._fused[key] = fp
+        return fp.run(points, n, self._threads)
+
     def close(self):
         for h in self._handles.values():
             h.close()
         self._handles.clear()
+        for p in self._paths.values():
+            p.close()
+        self._paths.clear()
+        for p in self._fused.values():
+            p.close()
+        self._fused.clear()
+        self._pool = []
 
 
 class VoxelGenerator_trt(VoxelGenerator):

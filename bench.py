@@ -54,6 +54,11 @@ def parse_args():
                     help="device-resident arm: front ends (workspace + graph) in flight; 1 = strictly serial steps (default: the "
                          "fill kernel fills the GPU, so a second batch in flight gains only ~5 %% at 20 cm and loses at 10 cm)")
     ap.add_argument("--pipelines", type=int, default=3, help="e2e: independent stream/workspace sets in flight")
+    ap.add_argument("--min-seconds", type=float, default=0.0,
+                    help="raise --steps until the timed region lasts at least this long (BASELINE configs[4]: >= 2 s)")
+    ap.add_argument("--sharded", action="store_true",
+                    help="single-process mode: ONE process drives --gpus N GPUs through the package's ShardedFrontEnd "
+                         "(one worker thread per GPU, numpy frames in, frame b -> GPU b mod N) instead of one rank per GPU")
     return ap.parse_args()
 
 
@@ -65,13 +70,33 @@ def dist_env():
 
 
 def spread_device(local, world, n_visible):
-    """GPU for local rank `local` when fewer ranks than GPUs run: alternate between the two halves of the box
-    (0, n/2, 1, n/2+1, ...) so that 2 or 4 ranks do not all hang off the same host bridge (PF_DEVICE_MAP=linear keeps
-    LOCAL_RANK -> GPU)."""
-    if os.environ.get("PF_DEVICE_MAP", "spread") == "linear" or world >= n_visible or n_visible % 2:
+    """GPU for local rank `local`: the package's bridge-aware placement (sharding.place_devices; PF_DEVICE_MAP=linear
+    keeps LOCAL_RANK -> GPU)."""
+    sh = importlib.import_module("3d_object_detection_b200.sharding")
+    if world > n_visible:
         return local
-    half = n_visible // 2
-    return (local % 2) * half + local // 2
+    return sh.place_devices(world, n_visible, os.environ.get("PF_DEVICE_MAP", "spread"))[local]
+
+
+def workload_config(grid, cfg, batch):
+    """The `config` object of the JSON line: ONE definition for both arms, so that the driver's same_config check compares
+    like with like.  Arm-specific details (pipelining, parallelism, measured voxel counts) live under `detail`."""
+    return {"workload": f"{grid}: batch {batch} x {cfg['frame_points']}-point synthetic frames per GPU (S1/S2/S3 mix), "
+                        f"voxelize+decorate+scatter, canvas ({batch},64,{cfg['_nx']},{cfg['_ny']}) fp32",
+            "grid": grid, "batch_per_gpu": batch, "frame_points": cfg["frame_points"], "max_voxels": cfg["max_voxels"],
+            "max_num_points": cfg["max_num_points"],
+            "l2": f"each step writes a {4 * 64 * cfg['_nx'] * cfg['_ny'] * batch / 1e6:.0f} MB canvas (> 126 MB L2), which "
+                  f"evicts the previous step's lines; no separate flush",
+            "e2e_io": "host points in (pinned), voxel counts + coordinates out; the canvas stays on the GPU for the backbone"}
+
+
+def load_workload(pfm, grid, batch_arg):
+    cfg = pfm.builtin_config(grid)
+    cfg["_name"] = grid
+    geom = pfm.derive_grid(cfg)
+    cfg["_nx"], cfg["_ny"] = int(geom.grid_size[0]), int(geom.grid_size[1])
+    batch = batch_arg or (32 if "10cm" in grid else 8)
+    return cfg, geom, batch
 
 
 def make_batch(pfm, cfg, geom, batch, rank):
@@ -159,33 +184,51 @@ class ClockSampler(threading.Thread):
 
 # ---------------------------------------------------------------------------------------------------------
 # CPU arm: the oracle port of the reference path (C, one frame per OpenMP thread) on the host cores
-def cpu_arm(cfg, geom, frames, pts_cat, offs, steps, warmup, budget_s):
+def cpu_arm(cfg, geom, frames, steps, warmup, budget_s, max_threads=None):
+    """K steps, each step = the batch of B frames the GPU arm runs.  The port is frame-parallel (one frame per OpenMP
+    thread), so m = cores // B steps run side by side (m * B frames per call) to occupy the host; a step is still B frames
+    and `steps_run` counts steps.  Stops early (>= 3 calls) when `budget_s` is spent."""
     from oracle import oracle          # bench.py's cpu_baseline / --impl reference legs may run the oracle
     b = len(frames)
     cores = os.cpu_count() or 1
-    threads = min(cores, b)
-    fb = oracle.FrontendBatch(geom, cfg["max_voxels"], cfg["max_num_points"], pts_cat.shape[1], b, 64)
+    if max_threads:
+        cores = min(cores, max_threads)
+    m = max(1, cores // b)
+    threads = min(cores, m * b)
     consts = oracle.decorate_consts(cfg["voxel_size"], geom.offset)
-    pillar = np.random.default_rng(1).standard_normal((b * cfg["max_voxels"], 64)).astype(np.float32)
-    offs64 = offs.astype(np.int64)
-    for _ in range(max(1, min(warmup, 2))):
-        fb.run(pts_cat, offs64, consts, pillar, threads)
-    times = []
+
+    def tile(k):
+        fr = frames * k
+        sizes = [len(f) for f in fr]
+        return (oracle.FrontendBatch(geom, cfg["max_voxels"], cfg["max_num_points"], frames[0].shape[1], k * b, 64),
+                np.concatenate(fr), np.concatenate([[0], np.cumsum(sizes)]).astype(np.int64),
+                np.random.default_rng(1).standard_normal((k * b * cfg["max_voxels"], 64)).astype(np.float32))
+
+    fb, pts, offs64, pillar = tile(m)
+    for _ in range(max(1, (warmup + m - 1) // m)):
+        fb.run(pts, offs64, consts, pillar, threads)
+    done, total = 0, 0.0
     t_start = time.perf_counter()
-    for i in range(steps):
+    calls = 0
+    while done < steps:
+        k = min(m, steps - done)
+        if k != m:
+            fb, pts, offs64, pillar = tile(k)
+            fb.run(pts, offs64, consts, pillar, min(threads, k * b))          # first touch of the new buffers, untimed
         t0 = time.perf_counter()
-        fb.run(pts_cat, offs64, consts, pillar, threads)
-        times.append(time.perf_counter() - t0)
-        if budget_s and time.perf_counter() - t_start > budget_s and i + 1 >= 3:
+        fb.run(pts, offs64, consts, pillar, min(threads, k * b))
+        total += time.perf_counter() - t0
+        done += k
+        calls += 1
+        if budget_s and time.perf_counter() - t_start > budget_s and calls >= 3:
             break
-    total = float(np.sum(times))
-    n_pts = int(pts_cat.shape[0]) * len(times)
+    n_pts = sum(len(f) for f in frames) * done
     return {"value": n_pts / total, "unit": UNIT, "cores": threads, "kind": "port",
-            "frames_per_s": b * len(times) / total, "ms_per_step": 1e3 * total / len(times),
-            "steps_run": len(times), "host_cores": cores,
-            "sample": f"{len(times)} batches of {b} frames x {len(frames[0])} points ({cfg['_name']} grid), "
-                      f"C oracle port of numba points_to_voxels + decoration + scatter, "
-                      f"one frame per thread on {threads} of {cores} host cores"}
+            "frames_per_s": b * done / total, "ms_per_step": 1e3 * total / done,
+            "steps_run": done, "host_cores": os.cpu_count() or 1,
+            "sample": f"{done} steps of {b} frames x {len(frames[0])} points ({cfg['_name']} grid), {m} steps side by side "
+                      f"per call, C oracle port of numba points_to_voxels + decoration + scatter, one frame per thread on "
+                      f"{threads} of {os.cpu_count() or 1} host cores"}
 
 
 def cpu_post_arm(cfg, geom, reps=3):
@@ -207,38 +250,23 @@ def cpu_post_arm(cfg, geom, reps=3):
 
 def run_reference(args, rank, world):
     """--impl reference: the reference's CPU implementation of the path (oracle port; the Python/numba reference
-    cannot travel to the GPU box) on the host cores.  Rank 0 only."""
+    cannot travel to the GPU box) on the host cores.  Rank 0 only.  Same `config`, `steps` and `warmup` as the b200 arm."""
     if rank != 0:
         return
     pfm = importlib.import_module("3d_object_detection_b200")
-    cfg = pfm.builtin_config(args.grid)
-    cfg["_name"] = args.grid
-    geom = pfm.derive_grid(cfg)
-    batch = args.batch or (32 if "10cm" in args.grid else 8)
-    frames, pts_cat, offs = make_batch(pfm, cfg, geom, batch, 0)
-    # bounded: K steps, each one batch; capped so the whole run stays within a few minutes
-    steps = max(1, min(args.steps, 40))
-    frames, pts_cat, offs = tile_for_cpu(frames, os.cpu_count() or 1)     # one frame per host thread
-    r = cpu_arm(cfg, geom, frames, pts_cat, offs, steps, args.warmup, budget_s=120.0)
+    cfg, geom, batch = load_workload(pfm, args.grid, args.batch)
+    frames, _, _ = make_batch(pfm, cfg, geom, batch, 0)
+    W = max(args.warmup, 3)
+    r = cpu_arm(cfg, geom, frames, args.steps, W, budget_s=150.0)
     line = {"impl": "reference", "metric": METRIC, "value": r["value"], "unit": UNIT, "n_gpus": args.gpus,
-            "steps": r["steps_run"], "warmup": min(args.warmup, 2), "ms_per_step": r["ms_per_step"],
+            "steps": r["steps_run"], "warmup": W, "ms_per_step": r["ms_per_step"],
             "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32",
             "data": "synthetic", "frames_per_s": r["frames_per_s"],
-            "config": {"workload": f"{args.grid}: batch {batch} x {cfg['frame_points']}-point synthetic frames "
-                                   f"(S1/S2/S3 mix), voxelize+decorate+scatter", "grid": args.grid,
-                       "batch_per_gpu": batch, "frame_points": cfg["frame_points"]},
-            "cpu_baseline": {k: r[k] for k in ("value", "unit", "cores", "kind", "sample")},
+            "config": workload_config(args.grid, cfg, batch),
+            "cpu_baseline": {k: r[k] for k in ("value", "unit", "cores", "kind", "sample", "host_cores")},
             "e2e": {"value": r["value"], "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
             "gpu_launches": 0}
     print(json.dumps(line), flush=True)
-
-
-def tile_for_cpu(frames, cores, cap=32):
-    """Give the CPU arm enough independent frames to occupy its cores (one frame per thread)."""
-    want = min(max(len(frames), cores), cap)
-    tiled = [frames[i % len(frames)] for i in range(want)]
-    sizes = [len(f) for f in tiled]
-    return tiled, np.concatenate(tiled), np.concatenate([[0], np.cumsum(sizes)]).astype(np.int32)
 
 
 # ---------------------------------------------------------------------------------------------------------
@@ -255,10 +283,7 @@ def run_b200(args, rank, world, local):
     if world > 1:
         dist.init_process_group("nccl", device_id=dev)
 
-    cfg = pfm.builtin_config(args.grid)
-    cfg["_name"] = args.grid
-    geom = pfm.derive_grid(cfg)
-    B = args.batch or (32 if "10cm" in args.grid else 8)
+    cfg, geom, B = load_workload(pfm, args.grid, args.batch)
     n_pts_frame = cfg["frame_points"]
     frames, pts_cat, offs = make_batch(pfm, cfg, geom, B, rank)
     n_points = int(pts_cat.shape[0])
@@ -289,7 +314,10 @@ def run_b200(args, rank, world, local):
         fe.replay()
     ev1.record()
     barrier()
-    t_serial = ev0.elapsed_time(ev1) * 1e-3
+    t_serial = ev0.elapsed_time(ev1) * 1e-3 / K        # seconds per step, strictly serial
+    if args.min_seconds > 0 and t_serial * K < args.min_seconds:      # same K on every rank: the estimate is reduced with MAX
+        est = importlib.import_module("3d_object_detection_b200.sharding").reduce_max_time(t_serial, dev)
+        K = int(np.ceil(args.min_seconds / est * 1.05))
     counts = fe.voxel_num.cpu().numpy()
     bytes_alg = fe.bytes_algorithmic(n_points, counts)
 
@@ -325,19 +353,20 @@ def run_b200(args, rank, world, local):
         assert p["fe"].voxel_num.cpu().numpy().tolist() == counts.tolist()
 
     # ---------------- per-stage timing (eager, CUDA events on the launch stream) ----------------
-    st = [torch.cuda.Event(enable_timing=True) for _ in range(3 * K)]
+    KS = min(K, 300)
+    st = [torch.cuda.Event(enable_timing=True) for _ in range(3 * KS)]
     for _ in range(3):
         fe.step(pts_d, offs_d, pillar_feats=pillar)
     torch.cuda.synchronize(dev)
-    for i in range(K):
+    for i in range(KS):
         st[3 * i].record()
         fe.voxelize_decorate(pts_d, offs_d)
         st[3 * i + 1].record()
         fe.scatter(pillar)
         st[3 * i + 2].record()
     torch.cuda.synchronize(dev)
-    t_vox = float(np.mean([st[3 * i].elapsed_time(st[3 * i + 1]) for i in range(K)])) * 1e-3
-    t_scat = float(np.mean([st[3 * i + 1].elapsed_time(st[3 * i + 2]) for i in range(K)])) * 1e-3
+    t_vox = float(np.mean([st[3 * i].elapsed_time(st[3 * i + 1]) for i in range(KS)])) * 1e-3
+    t_scat = float(np.mean([st[3 * i + 1].elapsed_time(st[3 * i + 2]) for i in range(KS)])) * 1e-3
 
     # ---------------- next-row N1: the learned PFN in the loop, fused vs torch (reported beside, not the headline) ----
     with_pfn = None
@@ -459,9 +488,29 @@ def run_b200(args, rank, world, local):
             for _ in range(reps):
                 one_frame(dev_out)
             lat[key + "_ms_per_frame"] = 1e3 * (time.perf_counter() - t0) / reps
+        def fused_frame():
+            canvas1, _, _ = vg.generate_and_scatter(frame0, net1)
+            torch.cuda.synchronize(dev)
+            return canvas1
+
+        def gen_only(dev_out):
+            return vg.generate(frame0, device_outputs=dev_out)
+
+        for key, fn in (("fused_generate_and_scatter_ms_per_frame", fused_frame),
+                        ("generate_only_numpy_ms_per_frame", lambda: gen_only(False)),
+                        ("generate_only_device_ms_per_frame", lambda: gen_only(True))):
+            with torch.no_grad():
+                for _ in range(5):
+                    fn()
+                t0 = time.perf_counter()
+                for _ in range(30):
+                    fn()
+            lat[key] = 1e3 * (time.perf_counter() - t0) / 30
         single = dict(lat, frame_points=int(len(frame0)),
-                      api="VoxelGenerator.generate(numpy points) -> PointNet.eval() (fused PFN) -> PointPillarsScatter, "
-                          "batch 1, host wall clock incl. H2D, the voxel-count read-back and a final synchronize")
+                      api="numpy_outputs / device_outputs: the reference's call sequence, VoxelGenerator.generate(numpy points) "
+                          "[-> example_convert_to_torch] -> PointNet.eval() (fused PFN) -> PointPillarsScatter, batch 1, host wall "
+                          "clock incl. staging, H2D, the voxel-count read-back and a final synchronize; fused_generate_and_scatter: "
+                          "the same work as ONE CUDA graph (VoxelGenerator.generate_and_scatter); generate_only_*: generate() alone")
         vg.close()
 
     # ---------------- end-to-end arm: public API, pinned host points in, coords/counts out ----------------
@@ -540,9 +589,54 @@ def run_b200(args, rank, world, local):
     if world > 1:
         dist.barrier()
         dist.destroy_process_group()
-    return dict(cfg=cfg, geom=geom, frames=frames, B=B, K=K, W=W, t_dev=t_dev, t_e2e=t_e2e, t_vox=t_vox,
+    fill_variant = int(importlib.import_module("3d_object_detection_b200._lib").load().pf_debug_set_fill_variant(
+        int(os.environ["PF_FILL_VARIANT"]) if os.environ.get("PF_FILL_VARIANT", "").isdigit() else -1))
+    return dict(fill_variant=fill_variant, cfg=cfg, geom=geom, frames=frames, B=B, K=K, W=W, t_dev=t_dev, t_e2e=t_e2e, t_vox=t_vox,
                 t_scat=t_scat, with_pfn=with_pfn, anchor=anchor, post=post, single=single, bound=bound, w_e2e=w_e2e, t_serial=t_serial, d_dev=d_dev, counts=counts, bytes_alg=bytes_alg, n_points=n_points, tot_pts=tot_pts,
                 tot_frames=tot_frames, clocks=clocks, h2d=h2d, d2h=d2h, fe=fe, depth=depth, world=world)
+
+
+def run_sharded(args):
+    """--sharded: the package-level multi-GPU runner.  One process, one worker thread per GPU (ShardedFrontEnd), host
+    numpy frames in (pageable, as a dataset hands them over), frame b -> GPU b mod N, pinned staging + one CUDA graph per
+    worker step, voxel counts back.  Wall clock over K steps is the end-to-end figure; the device figure is the MAX over
+    workers of their summed CUDA-event step times."""
+    import torch
+    pfm = importlib.import_module("3d_object_detection_b200")
+    G = args.gpus
+    cfg, geom, B = load_workload(pfm, args.grid, args.batch)
+    per_dev = [make_batch(pfm, cfg, geom, B, r)[0] for r in range(G)]
+    frames = [per_dev[b % G][b // G] for b in range(G * B)]          # frame b lands on worker b mod G
+    n_points = sum(len(f) for f in frames)
+    K, W = args.steps, max(args.warmup, 3)
+    with pfm.ShardedFrontEnd(cfg, devices=G, frames_per_device=B, max_points_per_frame=cfg["frame_points"], depth=2,
+                             stage_threads=max(1, min(4, (os.cpu_count() or 1) // max(G, 1)))) as sfe:
+        for _ in range(W):
+            sfe.run(frames)
+        sampler = ClockSampler(sfe.devices[0])
+        sampler.start()
+        t0 = time.perf_counter()
+        pending = [sfe.submit(frames) for _ in range(K)]
+        res = [[f.result() for f in futs] for futs in pending]
+        wall = time.perf_counter() - t0
+        clocks = sampler.stop()
+        dev_s = max(sum(step[i].device_ms for step in res) for i in range(G)) * 1e-3
+        counts = [int(c) for r in res[-1] for c in r.counts]
+        devices = list(sfe.devices)
+    line = {"metric": METRIC, "value": n_points * K / dev_s, "unit": UNIT, "n_gpus": G, "steps": K, "warmup": W,
+            "ms_per_step": 1e3 * dev_s / K, "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32",
+            "data": "synthetic", "frames_per_s": G * B * K / dev_s,
+            "mode": "single process, ShardedFrontEnd: one worker thread per GPU, no torch.distributed",
+            "config": workload_config(args.grid, cfg, B),
+            "detail": {"devices": devices, "voxels_per_frame_last_step": counts,
+                       "value_is": "points / MAX over workers of summed CUDA-event graph times (H2D + kernels + D2H of counts)"},
+            "e2e": {"value": n_points * K / wall, "unit": UNIT, "frames_per_s": G * B * K / wall, "ms_per_step": 1e3 * wall / K,
+                    "h2d_bytes_per_step": int(sum(f.nbytes for f in frames) // G), "d2h_bytes_per_step": 4 * B,
+                    "api": "ShardedFrontEnd.submit(list of pageable numpy frames): host staging copy into pinned memory, H2D, "
+                           "voxelise + decorate + canvas fill, D2H of the voxel counts; host wall clock over all K steps"},
+            "gpu_launches": K * G * (pfm.PillarFrontEnd.n_kernels_voxelize(cfg["frame_points"]) + 1),
+            "clocks": clocks}
+    print(json.dumps(line), flush=True)
 
 
 def peak_hbm_gbs():
@@ -555,10 +649,23 @@ def peak_hbm_gbs():
     return 6650.0, "fallback (B200_PROFILING.md 6.65 TB/s)"
 
 
+def host_link_ceiling(n_gpus):
+    """Aggregate copy-only pinned H2D GB/s for N concurrent GPUs from the committed probe (tools/h2d_ceiling.py), else None."""
+    for name in ("r2_h2d_ceiling.json", f"r2_h2d_ceiling_n{n_gpus}.json"):
+        try:
+            d = json.loads((ROOT / "profiles" / name).read_text())
+            for ln in d["lines"]:
+                if ln["n_gpus"] == n_gpus:
+                    return dict(ln, source=f"profiles/{name}")
+        except Exception:
+            continue
+    return None
+
+
 def ncu_traffic(grid, batch):
-    """DRAM bytes of one canvas-fill launch from the committed ncu capture of this workload, else None."""
+    """DRAM bytes of one canvas-fill launch from the committed ncu capture of this workload (shipped kernel set), else None."""
     try:
-        t = json.loads((ROOT / "profiles" / "r1_traffic.json").read_text()).get(f"{grid}:{batch}")
+        t = json.loads((ROOT / "profiles" / "r2_traffic.json").read_text()).get(f"{grid}:{batch}")
         return None if t is None else float(t["dram_read_bytes"]) + float(t["dram_write_bytes"])
     except Exception:
         return None
@@ -569,6 +676,10 @@ def main():
     rank, world, local = dist_env()
     if args.impl == "reference":
         run_reference(args, rank, world)
+        return
+    if args.sharded:
+        if rank == 0:
+            run_sharded(args)
         return
     r = run_b200(args, rank, world, local)
     if rank != 0:
@@ -586,17 +697,12 @@ def main():
         "dtype": "f32", "data": "synthetic",
         "frames_per_s": r["tot_frames"] / r["t_dev"],
         "device_pipelines": r["d_dev"],
-        "serial": {"ms_per_step": 1e3 * r["t_serial"] / K, "value": r["n_points"] * K / r["t_serial"], "unit": UNIT,
+        "serial": {"ms_per_step": 1e3 * r["t_serial"], "value": r["n_points"] / r["t_serial"], "unit": UNIT,
                    "note": "rank 0, one front end, step k+1 starts after step k's canvas is complete"},
-        "config": {"workload": f"{args.grid}: batch {B} x {cfg['frame_points']}-point synthetic frames per GPU "
-                               f"(S1/S2/S3 mix), voxelize+decorate+scatter, canvas ({B},64,{fe.nx},{fe.ny}) fp32",
-                   "grid": args.grid, "batch_per_gpu": B, "frame_points": cfg["frame_points"],
-                   "max_voxels": cfg["max_voxels"], "max_num_points": cfg["max_num_points"],
-                   "voxels_per_frame": r["counts"].tolist(), "parallelism": f"frame-sharded x{r['world']}, no collective",
+        "config": workload_config(args.grid, cfg, B),
+        "detail": {"voxels_per_frame": r["counts"].tolist(), "parallelism": f"frame-sharded x{r['world']}, no collective",
                    "pipelining": f"{r['d_dev']} batches in flight per GPU (own workspace, outputs and CUDA graph each); "
-                                 f"serial figure under 'serial'",
-                   "l2": f"each step writes a {4 * 64 * fe.nx * fe.ny * B / 1e6:.0f} MB canvas (> 126 MB L2), which "
-                         f"evicts the previous step's lines; no separate flush"},
+                                 f"serial figure under 'serial'", "fill_variant": r["fill_variant"]},
         "e2e": {"value": e2e_value, "unit": UNIT, "frames_per_s": r["tot_frames"] / r["t_e2e"],
                 "ms_per_step": 1e3 * r["t_e2e"] / K, "h2d_bytes_per_step": r["h2d"], "d2h_bytes_per_step": r["d2h"],
                 "api": "PillarFrontEnd.step on pinned host points; D2H of voxel_num + coordinates; canvas stays "
@@ -613,17 +719,24 @@ def main():
         "postprocess": r["post"],
         "single_frame_api": r["single"],
         "e2e_hbm_frac": r["bytes_alg"]["e2e"] / (r["t_dev"] / K) / 1e9 / peak,
-        "e2e_hbm_frac_serial": r["bytes_alg"]["e2e"] / (r["t_serial"] / K) / 1e9 / peak,
-        "roofline": {"kernel": "k_canvas_fill (pf_scatter_from_map)", "bound": "hbm", "achieved": achieved,
+        "e2e_hbm_frac_serial": r["bytes_alg"]["e2e"] / r["t_serial"] / 1e9 / peak,
+        "roofline": {"kernel": "k_canvas_fill<1,1,8> (pf_scatter_from_map, 32-byte streaming stores)", "bound": "hbm", "achieved": achieved,
                      "peak": peak, "unit": "GB/s", "frac": achieved / peak, "traffic": ncu_traffic(args.grid, B),
                      "peak_source": peak_src, "frac_of_nominal_8TBs": achieved / 8000.0,
                      "bytes_per_launch": scat_bytes, "ms_per_launch": 1e3 * r["t_scat"]},
     }
+    link = host_link_ceiling(r["world"])
+    if link is not None:
+        got = r["world"] * r["h2d"] / (r["t_e2e"] / K) / 1e9
+        line["e2e"]["roofline"] = {"bound": "host-link", "peak_gbs": link["aggregate_h2d_gbs"], "achieved_gbs": got,
+                                   "frac": got / link["aggregate_h2d_gbs"], "peak_source": link["source"],
+                                   "note": "aggregate pinned host->device GB/s of the e2e arm against what N copy-only "
+                                           "streams reach on this kind of box with no kernels running (tools/h2d_ceiling.py)"}
     if not args.no_cpu_baseline and r["world"] >= 1:
-        cores = os.cpu_count() or 1
-        tiled, pts_c, offs_c = tile_for_cpu(r["frames"], cores)
-        c = cpu_arm(cfg, r["geom"], tiled, pts_c, offs_c, steps=50, warmup=1, budget_s=args.cpu_seconds)
+        c = cpu_arm(cfg, r["geom"], r["frames"], steps=50, warmup=1, budget_s=args.cpu_seconds)
         line["cpu_baseline"] = {k: c[k] for k in ("value", "unit", "cores", "kind", "sample", "frames_per_s", "host_cores")}
+        c1 = cpu_arm(cfg, r["geom"], r["frames"][:1], steps=6, warmup=1, budget_s=min(6.0, args.cpu_seconds), max_threads=1)
+        line["cpu_baseline_1thread"] = {k: c1[k] for k in ("value", "unit", "cores", "kind", "sample", "frames_per_s")}
         if isinstance(line.get("postprocess"), dict) and "sparse" in line["postprocess"]:
             try:
                 line["postprocess"]["cpu_baseline"] = cpu_post_arm(cfg, r["geom"])

@@ -84,11 +84,24 @@ PF_API int pf_create(const pf_grid_desc *desc, int max_frames, int max_points_pe
 PF_API int pf_destroy(pf_handle *h);
 PF_API size_t pf_workspace_bytes(const pf_handle *h);
 
+/* Host helper of the single-frame drop-in path (VoxelGenerator.generate, framework/voxel_generator.py:28-40, is handed a
+ * pageable numpy array per frame): copies `bytes` from `src` to `dst` -- the caller's PINNED staging buffer -- with up to
+ * `threads` host threads (1..16), so that the host -> device copy that follows is one asynchronous DMA instead of the
+ * driver's synchronous staged copy.  Pure host code; touches no CUDA state. */
+PF_API int pf_stage_copy(void *dst, const void *src, size_t bytes, int threads);
+
 /* Diagnostics: with timing enabled every voxelise / fill call of this handle records a CUDA event after each of
  * its kernels (eager launches only -- do not capture such a call into a graph).  pf_debug_stage_times waits for
  * the last call and writes the 8 stage durations in milliseconds (quantize, assign, tile_rank, column_scan, slot,
  * gather, gap between gather and fill, canvas fill; -1 for a stage that did not run); returns the count. */
 PF_API int pf_debug_stage_timing(pf_handle *h, int enable);
+/* Diagnostics / A-B measurements: which kernel writes the canvas (process-wide; also the environment variable
+ * PF_FILL_VARIANT read at first use).  0 = one warp per 128 cells, 16-byte streaming stores; 1 = one warp per 256
+ * cells, 32-byte streaming stores (STG.256, the default); 2 = TMA bulk stores of shared-memory tiles (cp.async.bulk,
+ * UBLKCP), 512 bytes per copy; 3 = as 2 with an L2 evict-first hint; 4 / 5 = as 2 / 3 with 2 KB per copy; 6 = one warp
+ * per 512 cells, two 32-byte stores per lane and channel; -1 = the library default.  Every variant writes the same bytes.  Returns the
+ * variant now in force, or a negative pf_status. */
+PF_API int pf_debug_set_fill_variant(int variant);
 PF_API int pf_debug_stage_times(pf_handle *h, float *ms, int capacity);
 
 /* Output layouts (both written densely, padding rows zeroed):
@@ -104,7 +117,9 @@ PF_API int pf_debug_stage_times(pf_handle *h, float *ms, int capacity);
  *
  * points        device float [frame_offsets[n_frames]][point_stride] (first F floats of each row are used)
  * frame_offsets device int32 [n_frames+1], frame f is rows [frame_offsets[f], frame_offsets[f+1])
- * max_frame_points: host-side upper bound of any frame's size in this call (<= the handle's), sizes the grids.
+ * max_frame_points: host-side upper bound of any frame's size in this call (<= the handle's), sizes the grids.  A
+ *               frame whose device-side length exceeds it is processed up to this bound (its first
+ *               max_frame_points points), deterministically; nothing is read or written beyond it.
  */
 PF_API int pf_voxelize(pf_handle *h, const float *points, const int32_t *frame_offsets, int n_frames,
                 int max_frame_points, int point_stride, int compact, int coors_stride,

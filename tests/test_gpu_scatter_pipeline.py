@@ -76,6 +76,65 @@ def test_scatter_batched_and_backward(pf):
                               oracle.scatter(fe3, co3, nx3, ny3))
 
 
+@pytest.fixture
+def fill_variant(request):
+    """Select a canvas-fill kernel (pf_debug_set_fill_variant) for one test, then restore the library default."""
+    import importlib
+    L = importlib.import_module("3d_object_detection_b200._lib").load()
+    assert L.pf_debug_set_fill_variant(request.param) == request.param
+    yield request.param
+    L.pf_debug_set_fill_variant(-1)
+
+
+@pytest.mark.parametrize("fill_variant", [0, 1, 2, 3, 4, 5, 6], indirect=True)
+def test_fill_variants_write_the_same_canvas(pf, fill_variant):
+    """16-byte stores, 32-byte stores and the two TMA bulk-store kernels must produce identical canvases: the
+    reference-made hashes, a dense block (every cell of many 128 / 256-cell chunks occupied -> multi-pass staging),
+    a plane whose last chunk is partial (1000 x 1000), few channels, a batch, and the fused pipeline's cell map."""
+    for gkey, name in (("20cm", "s1"), ("nuscene", "s4_edges")):
+        g = util.load_small(gkey, name)
+        sc = pf.PointPillarsScatter(batch_size=1, output_shape=g["grid_size"], num_input_features=64)
+        feats, coors = torch.from_numpy(g["pillar_feats"]).cuda(), torch.from_numpy(g["coors"]).cuda()
+        for rep in range(2):
+            assert util.sha(_np(sc(feats, coors))) == str(g["canvas_sha"]), f"{gkey}/{name} rep {rep}"
+    rng = np.random.default_rng(17 + fill_variant)
+    nx = ny = 1000                                           # 16 cm grid: 1e6 cells = 7812.5 chunks of 128
+    for C, B in ((64, 2), (6, 3), (3, 1)):
+        coors, feats = [], []
+        for b in range(B):
+            bx, by = np.meshgrid(np.arange(300, 340), np.arange(500 + b, 548 + b), indexing="ij")     # dense 40 x 48 block
+            dense = bx.ravel() * ny + by.ravel()
+            tail = np.arange(nx * ny - 70, nx * ny)          # the partial last chunk, fully occupied
+            rest = rng.choice(nx * ny - 100, size=3000, replace=False)
+            cells = np.unique(np.concatenate([dense, tail, rest]))
+            rng.shuffle(cells)
+            coors.append(np.stack([cells // ny, cells % ny, np.zeros_like(cells), np.full_like(cells, b)], 1).astype(np.int32))
+            feats.append(rng.standard_normal((len(cells), C)).astype(np.float32))
+        coors, feats = np.concatenate(coors), np.concatenate(feats)
+        sc = pf.PointPillarsScatter(batch_size=B, output_shape=np.array([nx, ny, 1]), num_input_features=C)
+        for rep in range(2):
+            got = sc(torch.from_numpy(feats).cuda(), torch.from_numpy(coors if B > 1 else coors[:, :3]).cuda())
+            assert np.array_equal(_np(got), oracle.scatter(feats, coors, nx, ny, batch=B)), f"C={C} B={B} rep {rep}"
+    # the fused pipeline (MODE 1: the voxeliser's grid is the map), compact layout
+    cfg = cfgmod.builtin_config("20cm")
+    cfg["max_voxels"] = 3000
+    geom = cfgmod.derive_grid(cfg)
+    frames = [synth.make_frame(k, geom, n, 70 + i, 9) for i, (k, n) in enumerate([("S1", 9000), ("S3", 5000), ("S1", 4000)])]
+    fe = pf.PillarFrontEnd(cfg, max_batch=3, max_points_per_frame=9000, device=0, compact=True)
+    pts = torch.from_numpy(np.concatenate(frames)).cuda()
+    offs = torch.tensor(np.concatenate([[0], np.cumsum([len(f) for f in frames])]).astype(np.int32)).cuda()
+    pillar = torch.randn((3 * 3000, 64), device="cuda")
+    for rep in range(2):
+        canvas = fe.step(pts, offs, pillar_feats=pillar)
+        counts = _np(fe.voxel_num)
+        starts = np.concatenate([[0], np.cumsum(counts)])
+        for f in range(3):
+            sl = slice(int(starts[f]), int(starts[f + 1]))
+            want = oracle.scatter(_np(pillar[sl]), _np(fe.coors[sl])[:, :3], fe.nx, fe.ny)[0]
+            assert np.array_equal(_np(canvas[f]), want), f"pipeline frame {f} rep {rep}"
+    fe.close()
+
+
 @pytest.mark.parametrize("case", ["nuscene_s1", "20cm_s4_edges", "20cm_dup"])
 def test_scatter_backward_matches_reference_golden(pf, case):
     """Row A7 pinned: pf_scatter_backward through autograd against the gradient the REFERENCE's own
@@ -214,7 +273,8 @@ def test_pointnet_eval_mode_is_differentiable(pf):
     v, n, c = (torch.from_numpy(g[k]).cuda() for k in ("voxels", "num", "coors"))
     with torch.no_grad():
         fused = net(v, n, c)
-    assert fused.grad_fn is None and not net.wants_grad(v)
+        assert not net.wants_grad(v) and net.fusable(v)
+    assert fused.grad_fn is None and net.wants_grad(v)
     out = net(v, n, c)                                       # grad mode on, parameters require grad -> torch tail
     assert out.grad_fn is not None
     assert torch.allclose(out, fused, rtol=1e-4, atol=1e-3)
@@ -317,3 +377,36 @@ def test_kept_cell_map_must_be_consumed(pf):
     got = fe.step(pts, offs, pillar_feats=pillar)                     # and the handle still works, bit for bit
     assert torch.equal(got, want) and torch.equal(fe.voxel_num, want_counts)
     fe.close()
+
+
+def test_sharded_front_end_matches_oracle(pf):
+    """ShardedFrontEnd on the visible GPUs (one here, eight on a full box): frame b -> GPU b mod G, every canvas and
+    every coordinate list equal to the oracle's for that frame, ragged batch, two submissions in flight per worker."""
+    n_gpu = torch.cuda.device_count()
+    cfg = cfgmod.builtin_config("20cm")
+    cfg["max_voxels"] = 1500
+    geom = cfgmod.derive_grid(cfg)
+    B = 3
+    n_frames = n_gpu * B - 1
+    frames = [np.ascontiguousarray(synth.make_frame(["S1", "S3", "S2"][i % 3], geom, 3000 + 700 * (i % 4), 500 + i, 400))
+              for i in range(n_frames)]
+    with pf.ShardedFrontEnd(cfg, devices=n_gpu, frames_per_device=B, max_points_per_frame=6000, depth=2) as sfe:
+        assert len(sfe.workers) == n_gpu and sorted(sfe.devices) == list(range(n_gpu))
+        stand_in = []
+        for w in sfe.workers:                                 # seeded pillar stand-ins, as bench.py feeds the fill
+            for s in w.slots:
+                s["pillar"].copy_(torch.randn(s["pillar"].shape, generator=torch.Generator().manual_seed(w.device)).to(s["pillar"].device))
+            stand_in.append(w.slots[0]["pillar"].cpu().numpy())
+        first = sfe.submit(frames)
+        second = sfe.submit(frames[::-1])
+        for order, futs in ((frames, first), (frames[::-1], second)):
+            for wi, fut in enumerate(futs):
+                r = fut.result()
+                assert r.device == sfe.devices[wi] and r.canvas.device.index == r.device
+                for k, b in enumerate(r.frame_ids):
+                    v, c, n = oracle.generate(geom, order[b], cfg["max_voxels"], cfg["max_num_points"])
+                    assert int(r.counts[k]) == len(n)
+                    rows = slice(k * cfg["max_voxels"], k * cfg["max_voxels"] + len(n))
+                    assert np.array_equal(_np(r.coors[rows])[:, :3], c)
+                    want = oracle.scatter(stand_in[wi][rows], c, int(geom.grid_size[0]), int(geom.grid_size[1]))[0]
+                    assert np.array_equal(_np(r.canvas[k]), want), f"frame {b} on GPU {r.device}"

@@ -217,6 +217,59 @@ def test_shard_frames(pf):
         pf.shard_frames(4, 2, 2)
 
 
+def test_place_devices(pf):
+    """Bridge-aware placement (moved out of bench.py): fewer workers than GPUs alternate between the two halves."""
+    assert pf.place_devices(4, 8) == [0, 4, 1, 5] and pf.place_devices(2, 8) == [0, 4]
+    assert pf.place_devices(8, 8) == list(range(8)) and pf.place_devices(2, 4) == [0, 2]
+    assert pf.place_devices(1, 8) == [0] and pf.place_devices(2, 3) == [0, 1]
+    assert sorted(pf.place_devices(6, 8)) == [0, 1, 2, 4, 5, 6]
+    assert pf.place_devices(4, 8, "linear") == [0, 1, 2, 3]
+    with pytest.raises(ValueError):
+        pf.place_devices(9, 8)
+
+
+def test_sharded_front_end_scheduling(pf):
+    """ShardedFrontEnd without a GPU: frame b goes to worker b mod G, one worker thread per device runs its share,
+    results come back per device with the frame ids they cover, worker failures surface in the Future."""
+    import threading
+    import time
+
+    class FakeWorker:
+        def __init__(self, device):
+            self.device, self.calls, self.threads = device, [], set()
+
+        def run(self, ids, frames):
+            self.threads.add(threading.get_ident())
+            time.sleep(0.05)
+            if any(f is None for f in frames):
+                raise RuntimeError("bad frame")
+            self.calls.append(list(ids))
+            return (self.device, list(ids), [int(f.sum()) for f in frames])
+
+    frames = [np.full((3, 4), b, np.float32) for b in range(11)]
+    sfe = pf.ShardedFrontEnd({}, devices=[0, 4, 1], frames_per_device=4, _worker_factory=FakeWorker)
+    assert sfe.assignment(11) == [[0, 3, 6, 9], [1, 4, 7, 10], [2, 5, 8]]
+    assert sfe.assignment(2) == [[0], [1], []]
+    with pytest.raises(ValueError):
+        sfe.assignment(13)
+    t0 = time.perf_counter()
+    res = sfe.run(frames)
+    assert time.perf_counter() - t0 < 0.14                      # three 50 ms jobs ran side by side, not in sequence
+    assert [r[0] for r in res] == [0, 4, 1]
+    for r, ids in zip(res, sfe.assignment(11)):
+        assert r[1] == ids and r[2] == [12 * b for b in ids]
+    futs = sfe.submit(frames[:2])
+    assert futs[2] is None and futs[0].result()[1] == [0] and futs[1].result()[1] == [1]
+    main = threading.get_ident()
+    assert all(len(w.threads) == 1 and main not in w.threads for w in sfe.workers)
+    bad = sfe.submit([frames[0], None, frames[2]])
+    assert bad[0].result()[1] == [0]
+    with pytest.raises(RuntimeError, match="bad frame"):
+        bad[1].result()
+    assert sfe.run(frames[:3])[1][1] == [1]                     # the worker survived the failure
+    sfe.close()
+
+
 _GLOO_WORKER = r"""
 import importlib, json, os, sys
 sys.path.insert(0, sys.argv[1])

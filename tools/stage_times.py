@@ -38,7 +38,8 @@ net = pf.PointNet(4, cfg["voxel_size"], geom.offset).to(dev).eval() if a.pfn els
 lib = fe.handle.lib
 _lib.check(lib.pf_debug_stage_timing(fe.handle.ptr, 1))
 names = ["quantize(x2)", "assign", "tile_rank", "column_scan", "slot", "gather", "gap", "canvas_fill"]
-buf = (C.c_float * 8)()
+NS = len(names)
+buf = (C.c_float * NS)()
 acc = []
 with torch.no_grad():
     for s in range(a.samples + 3):
@@ -47,10 +48,10 @@ with torch.no_grad():
                 fe.step(pts, offs_d, pfn=net)
             else:
                 fe.step(pts, offs_d, pillar_feats=pillar)
-        n = lib.pf_debug_stage_times(fe.handle.ptr, buf, 8)
-        assert n == 8
+        n = lib.pf_debug_stage_times(fe.handle.ptr, buf, NS)
+        assert n == NS
         if s >= 3:
-            acc.append([buf[i] * 1e3 for i in range(8)])
+            acc.append([max(buf[i], 0.0) * 1e3 for i in range(NS)])
 acc = np.asarray(acc)
 print(f"{a.grid} batch {B}{' fused PFN' if a.pfn else ''}: per-kernel us inside the step (mean / min of {a.samples} samples)")
 for i, nm in enumerate(names):
