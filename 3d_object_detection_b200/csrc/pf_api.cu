@@ -52,6 +52,23 @@ inline size_t align_up(size_t x, size_t a) { return (x + a - 1) / a * a; }
 
 bool aligned16(const void *p) { return (reinterpret_cast<uintptr_t>(p) & 15) == 0; }
 
+// 0 when the gather / decoration kernel for (P, F) fits the opt-in shared memory of `device` (< 0: current), else the
+// PF_ERR_UNSUPPORTED status (message set)
+int check_gather_shape(int P, int F, int device, const char *who)
+{
+    if (device < 0 && cudaGetDevice(&device) != cudaSuccess) return 0;   // no device yet: the launch will report it
+    int limit = 0;
+    if (cudaDeviceGetAttribute(&limit, cudaDevAttrMaxSharedMemoryPerBlockOptin, device) != cudaSuccess) {
+        cudaGetLastError();
+        return 0;
+    }
+    const size_t need = pf::gather_smem_needed(P, F);
+    if (need > (size_t)limit)
+        return fail(PF_ERR_UNSUPPORTED, "%s: max_points %d with %d floats per point needs %zu bytes of shared memory per CTA, the "
+                                        "device allows %d", who, P, F, need, limit);
+    return 0;
+}
+
 // NVTX range around the enqueue of one C-ABI call (keep the path visible in traces)
 struct Range {
     explicit Range(const char *name) { nvtxRangePushA(name); }
@@ -101,6 +118,7 @@ int pf_create(const pf_grid_desc *d, int max_frames, int max_points_per_frame, i
         if (e != cudaSuccess) return cuda_fail(e, "pf_create: cudaGetDevice");
     }
     DeviceGuard guard(device);
+    if (int rc = check_gather_shape(d->max_points, d->num_features, device, "pf_create")) return rc;
 
     pf_handle *h = new (std::nothrow) pf_handle();
     if (!h) return fail(PF_ERR_OUT_OF_MEMORY, "pf_create: host allocation failed");
@@ -206,6 +224,21 @@ int pf_stage_copy(void *dst, const void *src, size_t bytes, int threads)
     for (int t = 0; t < threads; ++t) {
         const size_t lo = (size_t)t * chunk;
         if (lo < bytes) memcpy(static_cast<char *>(dst) + lo, static_cast<const char *>(src) + lo, bytes - lo < chunk ? bytes - lo : chunk);
+    }
+    return PF_OK;
+}
+
+int pf_copy3(void *dst0, const void *src0, size_t bytes0, void *dst1, const void *src1, size_t bytes1, void *dst2,
+             const void *src2, size_t bytes2, void *stream)
+{
+    void *d[3] = {dst0, dst1, dst2};
+    const void *s[3] = {src0, src1, src2};
+    const size_t b[3] = {bytes0, bytes1, bytes2};
+    for (int k = 0; k < 3; ++k) {
+        if (b[k] == 0) continue;
+        if (!d[k] || !s[k]) return fail(PF_ERR_INVALID_ARGUMENT, "pf_copy3: null pointer in copy %d", k);
+        cudaError_t e = cudaMemcpyAsync(d[k], s[k], b[k], cudaMemcpyDefault, static_cast<cudaStream_t>(stream));
+        if (e != cudaSuccess) return cuda_fail(e, "pf_copy3");
     }
     return PF_OK;
 }
@@ -331,6 +364,7 @@ int pf_decorate(const float *voxels, const int32_t *num_points, const int32_t *c
     if (max_points < 1 || max_points > 4096) return fail(PF_ERR_UNSUPPORTED, "pf_decorate: max_points %d outside 1..4096", max_points);
     if (num_features < 3 || num_features > 16) return fail(PF_ERR_UNSUPPORTED, "pf_decorate: num_features %d outside 3..16", num_features);
     if (!aligned16(features)) return fail(PF_ERR_INVALID_ARGUMENT, "pf_decorate: features must be 16-byte aligned");
+    if (int rc = check_gather_shape(max_points, num_features, -1, "pf_decorate")) return rc;
     Range nvtx_range("pf_decorate");
     cudaError_t e = pf::launch_decorate(voxels, num_points, coors, coors_stride, n_voxels, max_points, num_features, vx, vy,
                                         x_off, y_off, features, static_cast<cudaStream_t>(stream));

@@ -127,6 +127,7 @@ cudaError_t launch_anchor_mask(const int32_t *coors, int coors_stride, const int
                                long long n_anchors, int32_t *integral, uint8_t *mask, int *table_is_u16,
                                cudaStream_t stream);
 
+size_t gather_smem_needed(int P, int F);   // pf_voxelize.cu
 int fill_variant();            // pf_scatter.cu: which canvas-fill kernel runs (see pf_debug_set_fill_variant)
 void set_fill_variant(int v);
 

@@ -12,7 +12,8 @@
 
 namespace pf {
 
-constexpr int kFillDefault = 1;   // 32-byte stores: 242 vs 255 us at 20 cm x 8, 3.34 vs 3.59 ms at 10 cm x 32 (profiles/r2_fill_variants.md)
+constexpr int kFillDefault = -1;   // auto: 32-byte stores, one warp per 256 cells, or per 512 cells on canvases of >= 2^25 cells
+                                   // (profiles/r2_fill_variants.md: 20 cm x 8 238 vs 239 us, nuScenes x 8 109 vs 118 us, 10 cm x 32 3281 vs 3176 us)
 
 // map[b][x*ny+y] = max(row) over pillars in that cell  (highest row wins == sequential index_put)
 __global__ void __launch_bounds__(256) k_map_index(const int32_t *__restrict__ coors, int coors_stride,
@@ -386,16 +387,18 @@ __global__ void __launch_bounds__(256) k_scatter_backward(const float *__restric
 // fill variants (pf_debug_set_fill_variant / PF_FILL_VARIANT): 0 = warp, 16-byte stores (round 1's kernel), 1 = warp,
 // 32-byte stores, 2 / 3 = TMA bulk stores of 512 bytes (3: L2 evict-first hint), 4 / 5 = TMA bulk stores of 2 KB
 static int g_fill_variant = -1;
+static bool g_fill_set = false;
 
 int fill_variant()
 {
-    if (g_fill_variant < 0) {
+    if (!g_fill_set) {
         const char *e = getenv("PF_FILL_VARIANT");
         g_fill_variant = (e && e[0] >= '0' && e[0] <= '6') ? e[0] - '0' : kFillDefault;
+        g_fill_set = true;
     }
     return g_fill_variant;
 }
-void set_fill_variant(int v) { g_fill_variant = (v >= 0 && v <= 6) ? v : kFillDefault; }
+void set_fill_variant(int v) { g_fill_variant = (v >= 0 && v <= 6) ? v : kFillDefault, g_fill_set = true; }
 
 template <int MODE>
 static cudaError_t run_fill(int32_t *map, const float *feats, int64_t sv, int64_t sc, const int32_t *vnum,
@@ -412,7 +415,8 @@ static cudaError_t run_fill(int32_t *map, const float *feats, int64_t sv, int64_
         k_map_reset<<<148 * 4, 256, 0, stream>>>(map, (size_t)batch * plane, MODE == 0 ? -1 : kEmpty);
         return cudaGetLastError();
     }
-    const int variant = fill_variant();
+    int variant = fill_variant();
+    if (variant < 0) variant = ((long long)batch * plane >= (1ll << 25)) ? 6 : 1;
     const bool feat4 = (sc == 1) && (sv % 4 == 0) && (n_ch % 4 == 0) && ((reinterpret_cast<uintptr_t>(feats) & 15) == 0);
     if (variant >= 2 && variant <= 5) {
         // 2: 128-cell chunks x 64 channels (512-byte copies); 3: the same + L2 evict-first; 4: 512-cell chunks x 16 channels
@@ -438,7 +442,8 @@ static cudaError_t run_fill(int32_t *map, const float *feats, int64_t sv, int64_
         }
     }
     const bool al32 = (reinterpret_cast<uintptr_t>(canvas) & 31) == 0;
-    if (variant == 6 && (plane % 16 == 0) && al32) {   // 512 cells per warp, 4 warps per CTA, two 32-byte stores per lane and channel
+    if (variant == 6 && (plane % 16 != 0 || !al32)) variant = 1;
+    if (variant == 6) {   // 512 cells per warp, 4 warps per CTA, two 32-byte stores per lane and channel
         const long long warps6 = (long long)((plane + 511) / 512) * batch;
         const unsigned blocks6 = (unsigned)((warps6 + 3) / 4);
         if (feat4)
@@ -447,7 +452,7 @@ static cudaError_t run_fill(int32_t *map, const float *feats, int64_t sv, int64_
             k_canvas_fill<MODE, false, 16, 4, 2304><<<blocks6, 128, 0, stream>>>(map, feats, sv, sc, vnum, max_voxels, compact, batch, n_ch, plane, canvas);
         return cudaGetLastError();
     }
-    const bool wide = variant == 1 && (plane % 8 == 0) && al32;
+    const bool wide = variant == 1 && (plane % 8 == 0) && al32;   // else variant 0
     const int wcells = wide ? 256 : 128;
     const long long warps = (long long)((plane + wcells - 1) / wcells) * batch;
     const unsigned blocks = (unsigned)((warps + kFillWarps - 1) / kFillWarps);

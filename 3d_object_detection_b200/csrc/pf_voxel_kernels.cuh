@@ -3,7 +3,7 @@
 //
 // Order-free definition implemented here (checked on the CPU by oracle/spec_parallel.py):
 //   first[c]  = lowest index of an inside point in cell c                          (k_quantize, atomicMin)
-//   creator i = first[cell_i] == i ; voxel id = exclusive scan of creator flags     (k_order, phases A-C)
+//   creator i = first[cell_i] == i ; voxel id = exclusive scan of creator flags     (k_assign, one pass)
 //   i*        = the creator whose id equals max_voxels (the loop's `break`), else N
 //   slot of i = number of earlier points of the same voxel, from a (tile x voxel) count matrix with a
 //               saturating column scan                                           (k_tile_rank, k_column_scan)
@@ -46,7 +46,7 @@ __global__ void __launch_bounds__(256) k_quantize(Params p, Work w, const float 
     const int n_all = frame_offsets[f + 1] - base;
     const int n = n_all < hi ? n_all : hi;     // this launch covers [lo, min(n, hi)); hi <= the call's max_frame_points
     const int i0 = lo + blockIdx.x * (256 * kQPer) + threadIdx.x;
-    if (lo == 0 && blockIdx.x == 0) {          // per-call state of k_order: tile tickets, look-back words
+    if (lo == 0 && blockIdx.x == 0) {          // per-call state of k_assign: tile tickets, look-back words
         if (threadIdx.x == 0) {
             w.ticket[f] = 0;
             w.istar[f] = 0x7fffffff;   // "no break" default; k_assign lowers it on max_voxels overflow
@@ -306,9 +306,68 @@ __global__ void __launch_bounds__(kTileWarps * 32) k_tile_rank(Params p, Work w,
 
 // ---------------------------------------------------------------------------------------------------------
 // K5: saturating exclusive scan down every voxel column of the count matrix (in place), totals -> vcount.
-// A thread owns 4 adjacent columns (one 32-bit word per row); rows are independent loads.
-__global__ void __launch_bounds__(128) k_column_scan(Params p, Work w, const int32_t *__restrict__ frame_offsets,
-                                                     int max_frame_points)
+// A warp owns 32 adjacent 4-column words (128 voxels); the S warps of a CTA split the rows (tiles) of those columns into
+// S slices of <= 16 rows, so every thread issues ALL its loads at once (one L2 round trip instead of rows / 16 of them --
+// the round-1 kernel, one thread per word walking all rows, was latency-bound at 10 us for 7.5 MB), reduces its slice with
+// per-byte saturating adds, and picks its starting value from the slice totals of the warps in front of it.
+constexpr int kScanRows = 16;
+
+__global__ void __launch_bounds__(512) k_column_scan(Params p, Work w, const int32_t *__restrict__ frame_offsets,
+                                                      int max_frame_points)
+{
+    __shared__ uint32_t s_part[16][33];
+    const int f = blockIdx.y;
+    int n = frame_offsets[f + 1] - frame_offsets[f];
+    if (n > max_frame_points) n = max_frame_points;
+    const int n_tiles = (n + kTile - 1) / kTile;
+    const int n_vox = w.vnum[f];
+    const int lane = threadIdx.x & 31, slice = threadIdx.x >> 5, n_slices = blockDim.x >> 5;
+    const int col = (blockIdx.x * 32 + lane) * 4;
+    if (blockIdx.x * 128 >= n_vox) return;            // block-uniform
+    const bool active = col < n_vox;
+    uint32_t *m = reinterpret_cast<uint32_t *>(w.cnt + (size_t)f * p.tiles_cap * p.vcols + col);
+    const size_t row_words = p.vcols / 4;
+    const int rows = (n_tiles + n_slices - 1) / n_slices;     // <= kScanRows: the launcher sizes n_slices for it
+    const int t0 = slice * rows;
+    const int t1 = (t0 + rows) < n_tiles ? (t0 + rows) : n_tiles;
+    uint32_t v[kScanRows];
+#pragma unroll
+    for (int u = 0; u < kScanRows; ++u) v[u] = (active && t0 + u < t1) ? m[(size_t)(t0 + u) * row_words] : 0u;
+    uint32_t tot = 0;
+#pragma unroll
+    for (int u = 0; u < kScanRows; ++u) tot = __vaddus4(tot, v[u]);      // per-byte saturating add: caps at kCountCap = 255
+    s_part[slice][lane] = tot;
+    __syncthreads();
+    uint32_t run = 0;
+    for (int s = 0; s < slice; ++s) run = __vaddus4(run, s_part[s][lane]);
+    if (!active) return;
+#pragma unroll
+    for (int u = 0; u < kScanRows; ++u) {
+        if (t0 + u < t1) {
+            m[(size_t)(t0 + u) * row_words] = run;
+            run = __vaddus4(run, v[u]);
+        }
+    }
+    if (slice == n_slices - 1) {
+#pragma unroll
+        for (int k = 0; k < 4; ++k) {
+            const int c = (int)((run >> (8 * k)) & 0xffu);
+            if (col + k < n_vox) w.vcount[(size_t)f * p.max_voxels + col + k] = c < p.P ? c : p.P;
+        }
+    }
+}
+
+// the launch shape of k_column_scan for frames of up to `tiles` tiles: warps (= row slices) per CTA, or 0 when a frame
+// is too long for <= kScanRows rows per slice with 16 slices (> 524 288 points): the caller falls back to the serial kernel
+inline int column_scan_slices(int tiles)
+{
+    const int s = (tiles + kScanRows - 1) / kScanRows;
+    return s < 1 ? 1 : (s > 16 ? 0 : s);
+}
+
+// one thread per 4-column word walking all rows, 16 loads in flight: any frame length
+__global__ void __launch_bounds__(128) k_column_scan_serial(Params p, Work w, const int32_t *__restrict__ frame_offsets,
+                                                            int max_frame_points)
 {
     const int f = blockIdx.y;
     int n = frame_offsets[f + 1] - frame_offsets[f];
@@ -319,7 +378,7 @@ __global__ void __launch_bounds__(128) k_column_scan(Params p, Work w, const int
     if (col >= n_vox) return;
     uint32_t *m = reinterpret_cast<uint32_t *>(w.cnt + (size_t)f * p.tiles_cap * p.vcols + col);
     const size_t row_words = p.vcols / 4;
-    int run[4] = {0, 0, 0, 0};
+    uint32_t run = 0;
     constexpr int U = 16;
     for (int t0 = 0; t0 < n_tiles; t0 += U) {
         uint32_t v[U];
@@ -328,20 +387,16 @@ __global__ void __launch_bounds__(128) k_column_scan(Params p, Work w, const int
 #pragma unroll
         for (int u = 0; u < U; ++u) {
             if (t0 + u < n_tiles) {
-                uint32_t out = 0;
-#pragma unroll
-                for (int k = 0; k < 4; ++k) {
-                    out |= (uint32_t)run[k] << (8 * k);
-                    const int s = run[k] + (int)((v[u] >> (8 * k)) & 0xffu);
-                    run[k] = s < kCountCap ? s : kCountCap;
-                }
-                m[(size_t)(t0 + u) * row_words] = out;
+                m[(size_t)(t0 + u) * row_words] = run;
+                run = __vaddus4(run, v[u]);
             }
         }
     }
 #pragma unroll
-    for (int k = 0; k < 4; ++k)
-        if (col + k < n_vox) w.vcount[(size_t)f * p.max_voxels + col + k] = run[k] < p.P ? run[k] : p.P;
+    for (int k = 0; k < 4; ++k) {
+        const int c = (int)((run >> (8 * k)) & 0xffu);
+        if (col + k < n_vox) w.vcount[(size_t)f * p.max_voxels + col + k] = c < p.P ? c : p.P;
+    }
 }
 
 // ---------------------------------------------------------------------------------------------------------

@@ -166,6 +166,21 @@ __global__ void __launch_bounds__(256) k_gather(Params p, Work w, GatherArgs a)
 
 // ---------------------------------------------------------------------------------------------------------
 // host-side launchers
+// Dynamic shared memory of the gather / decoration kernel a shape would be launched with (the F = 4 fast path of
+// pf_gather.cu for P <= 512, else the generic kernel above): what the C ABI checks against the device's opt-in limit at
+// validation time, so that an oversized (P, F) is refused as PF_ERR_UNSUPPORTED instead of failing at launch.
+size_t gather_smem_needed(int P, int F)
+{
+    if (F == 4 && P <= 512) {
+        const int vpw = (P == 15 || P == 10) ? 8 : (P == 100 ? 1 : (P <= 16 ? 2 : 1));
+        return (size_t)8 * (((size_t)vpw * P * 9 + 4 + 3) & ~(size_t)3) * sizeof(float);
+    }
+    const int vpb = 256 / (P <= 16 ? 16 : 32);
+    const size_t a = ((size_t)vpb * P * F + 4 + 3) & ~(size_t)3;
+    const size_t b = (size_t)vpb * P * (F + 5) + 4;
+    return (a + b) * sizeof(float);
+}
+
 static size_t gather_smem_bytes(int group, int P, int F)
 {
     const int vpb = 256 / group;
@@ -228,7 +243,10 @@ cudaError_t launch_voxelize(const Params &p, const Work &w, const VoxelizeArgs &
     }
     k_tile_rank<<<g_tiles, kTileWarps * 32, p.vcols, stream>>>(p, w, a.frame_offsets, npts);
     mark(w, kEvTileRank, stream);
-    k_column_scan<<<dim3((p.vcols / 4 + 127) / 128, B), 128, 0, stream>>>(p, w, a.frame_offsets, npts);
+    if (const int slices = column_scan_slices(tiles))
+        k_column_scan<<<dim3((p.vcols / 4 + 31) / 32, B), 32 * slices, 0, stream>>>(p, w, a.frame_offsets, npts);
+    else
+        k_column_scan_serial<<<dim3((p.vcols / 4 + 127) / 128, B), 128, 0, stream>>>(p, w, a.frame_offsets, npts);
     mark(w, kEvColumnScan, stream);
     k_slot<<<g_pts, 256, 0, stream>>>(p, w, a.frame_offsets, npts, a.keep_cell_map ? 0 : 1);
     mark(w, kEvSlot, stream);

@@ -39,12 +39,14 @@ class FusedFramePath:
     def _graph(self, rows: int):
         g = self.graphs.get(rows)
         if g is None:
+            torch.cuda.synchronize(self.dev)
             with torch.cuda.device(self.dev), torch.cuda.stream(self.stream), torch.no_grad():
                 self._body(rows)
                 self.stream.synchronize()
                 g = torch.cuda.CUDAGraph()
                 with torch.cuda.graph(g, stream=self.stream):
                     self._body(rows)
+            torch.cuda.synchronize(self.dev)
             self.graphs[rows] = g
         return g
 
@@ -56,12 +58,8 @@ class FusedFramePath:
         self.np_offs[1] = n
         rows = min(self.cap, max(4096, (n + 4095) // 4096 * 4096))
         g = self._graph(rows)
-        cur = torch.cuda.current_stream(self.dev)
-        self.stream.wait_stream(cur)                  # the consumer of the previous canvas may still be reading it
-        with torch.cuda.stream(self.stream):
-            g.replay()
-            self.event.record(self.stream)
-        cur.wait_event(self.event)
+        g.replay()                                    # on the caller's current stream: ordered behind the consumer of the
+        self.event.record(torch.cuda.current_stream(self.dev))      # previous canvas, in front of the consumer of this one
         self.event.synchronize()
         v = int(self.np_vnum[0])
         return self.fe.canvas, self.fe.coors[:v], v

@@ -141,10 +141,15 @@ class PillarFrontEnd:
                                          0 if self.compact else self.max_voxels)
 
     # ---- CUDA graph of a fixed-shape step --------------------------------------------------------
-    def capture(self, points, frame_offsets, pillar_feats=None, pfn=None):
+    def capture(self, points, frame_offsets, pillar_feats=None, pfn=None, chain_priority=False):
         """Capture step() for these (static) tensors; replay() re-runs it on whatever they then contain.  With ``pfn``
         (a PointNet in eval mode) the fused voxelise + decorate + PFN kernel is captured; its folded weights are
-        read at capture time."""
+        read at capture time.
+
+        ``chain_priority``: capture the voxelise chain on a HIGH-priority stream and the canvas fill on a normal one
+        (fork / join inside the graph).  When several front ends replay on different streams -- batch k+1's chain while
+        batch k's fill is still streaming out -- the latency-bound chain kernels are then scheduled ahead of the fill's
+        thousands of CTAs instead of queueing behind them."""
         self._g_inputs = (points, frame_offsets, pillar_feats, pfn)
         side = torch.cuda.Stream(self.device)
         side.wait_stream(torch.cuda.current_stream(self.device))
@@ -154,8 +159,27 @@ class PillarFrontEnd:
         torch.cuda.current_stream(self.device).wait_stream(side)
         torch.cuda.synchronize(self.device)
         g = torch.cuda.CUDAGraph()
-        with torch.cuda.graph(g), torch.no_grad():
-            self.step(points, frame_offsets, pillar_feats=pillar_feats, pfn=pfn)
+        if not chain_priority:
+            with torch.cuda.graph(g), torch.no_grad():
+                self.step(points, frame_offsets, pillar_feats=pillar_feats, pfn=pfn)
+        else:
+            lo, hi_prio = torch.cuda.Stream.priority_range() if hasattr(torch.cuda.Stream, "priority_range") else (0, -1)
+            hi = torch.cuda.Stream(self.device, priority=hi_prio)
+            cap = torch.cuda.Stream(self.device)
+            fused = (pfn is not None and hasattr(pfn, "folded") and self.F == 4 and
+                     (pfn.fusable() if hasattr(pfn, "fusable") else not getattr(pfn, "training", True)))
+            with torch.cuda.graph(g, stream=cap), torch.no_grad():
+                hi.wait_stream(cap)                                   # fork
+                with torch.cuda.stream(hi):
+                    if fused:
+                        feats = self.voxelize_pfn(points, frame_offsets, pfn.folded())
+                    else:
+                        self.voxelize_decorate(points, frame_offsets)
+                        feats = pillar_feats
+                        if pfn is not None:
+                            feats = pfn.features_to_pillars(self.features) if hasattr(pfn, "features_to_pillars") else pfn(self.features)
+                cap.wait_stream(hi)                                   # join
+                self.scatter(feats)
         self._graph = g
         return g
 

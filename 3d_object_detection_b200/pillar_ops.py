@@ -166,9 +166,10 @@ _SCATTER_HANDLES = {}
 
 
 def _scatter_handle(nx: int, ny: int, batch: int, device: torch.device) -> "_lib.Handle":
-    """Workspace holding the cell->row map for a stand-alone scatter (one per device / plane / batch)."""
+    """Workspace holding the cell->row map for a stand-alone scatter: one per (device, STREAM, plane) -- a handle is
+    not re-entrant (include/pillarfront.h), and two modules running on different streams must not share one map."""
     idx = device.index if device.index is not None else torch.cuda.current_device()
-    key = (idx, nx, ny)
+    key = (idx, torch.cuda.current_stream(idx).cuda_stream, nx, ny)
     h = _SCATTER_HANDLES.get(key)
     if h is None or h.max_frames < batch:
         if h is not None:

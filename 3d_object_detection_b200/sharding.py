@@ -61,7 +61,8 @@ def place_devices(n_workers: int, n_visible: int, mode: str = "spread"):
 class ShardResult:
     """What one GPU produced for its share of a submitted batch.  `canvas` (n, C, nx, ny), `coors` (n * max_voxels, 4)
     and `voxel_num` (n,) are CUDA tensors on `device`, views of the worker's buffers: valid until that worker has been
-    handed `depth` further batches.  `counts` is `voxel_num` on the host."""
+    handed `depth - 1` further batches (the worker stages batch k+1 while batch k runs, so depth >= 2; the default is 3).
+    `counts` is `voxel_num` on the host."""
 
     __slots__ = ("device", "frame_ids", "canvas", "coors", "voxel_num", "counts", "device_ms")
 
@@ -71,9 +72,9 @@ class ShardResult:
 
 
 class _GpuWorker:
-    """One GPU: `depth` PillarFrontEnd replicas (workspace, outputs, pinned staging, one CUDA graph each), used in
-    turn; the graph holds H2D of the staged frames + offsets, voxelise + decorate (+ fused PFN), canvas fill, D2H of
-    the voxel counts."""
+    """One GPU: `depth` PillarFrontEnd replicas (workspace, outputs, pinned staging, one stream and one CUDA graph
+    each), used in turn; the graph holds H2D of the staged frames + offsets, voxelise + decorate (+ fused PFN), canvas
+    fill, D2H of the voxel counts."""
 
     def __init__(self, config, device, frames_per_device, max_points_per_frame, n_channels, pfn, depth, stage_threads):
         import copy
@@ -92,7 +93,6 @@ class _GpuWorker:
         self.slots = []
         with torch.cuda.device(dev):
             self.pfn = copy.deepcopy(pfn).to(dev).eval() if pfn is not None else None
-            self.stream = torch.cuda.Stream(dev)
             for _ in range(depth):
                 fe = PillarFrontEnd(config, max_batch=self.B, max_points_per_frame=self.cap, device=self.device,
                                     n_channels=self.C, want_voxels=False)
@@ -102,13 +102,14 @@ class _GpuWorker:
                          d_pts=torch.empty((self.B * self.cap, self.F), dtype=torch.float32, device=dev),
                          d_offs=torch.zeros((self.B + 1,), dtype=torch.int32, device=dev),
                          pillar=None if self.pfn is not None else torch.zeros((self.B * fe.max_voxels, self.C), device=dev),
-                         e0=torch.cuda.Event(enable_timing=True), e1=torch.cuda.Event(enable_timing=True))
+                         e0=torch.cuda.Event(enable_timing=True), e1=torch.cuda.Event(enable_timing=True),
+                         stream=torch.cuda.Stream(dev))       # one stream per slot: the H2D of batch k+1 runs under the kernels of batch k
                 s["np_pts"], s["np_offs"], s["np_cnt"] = s["h_pts"].numpy(), s["h_offs"].numpy(), s["h_cnt"].numpy()
-                with torch.cuda.stream(self.stream), torch.no_grad():
+                with torch.cuda.stream(s["stream"]), torch.no_grad():
                     self._body(s)
-                    self.stream.synchronize()
+                    s["stream"].synchronize()
                     s["graph"] = torch.cuda.CUDAGraph()
-                    with torch.cuda.graph(s["graph"], stream=self.stream):
+                    with torch.cuda.graph(s["graph"], stream=s["stream"]):
                         self._body(s)
                 self.slots.append(s)
         self.turn = 0
@@ -122,8 +123,9 @@ class _GpuWorker:
             s["fe"].step(s["d_pts"], s["d_offs"], pillar_feats=s["pillar"])
         s["h_cnt"].copy_(s["fe"].voxel_num, non_blocking=True)
 
-    def run(self, frame_ids, frames):
-        """Stage `frames` (list of (N, F) float32 arrays, at most B of them), replay, wait, return a ShardResult."""
+    def launch(self, frame_ids, frames):
+        """Stage `frames` (list of (N, F) float32 arrays, at most B of them) into the next slot's pinned buffer and
+        enqueue that slot's graph; returns a token for :meth:`finish`.  Does not wait for the GPU."""
         torch = self.torch
         s = self.slots[self.turn % len(self.slots)]
         self.turn += 1
@@ -137,8 +139,8 @@ class _GpuWorker:
             offs[b] = pos
             if b < n:
                 f = frames[b]
-                if str(f.dtype) != "float32":
-                    raise TypeError(f"frames must be float32 numpy arrays, got {f.dtype}")
+                if str(getattr(f, "dtype", None)) != "float32":
+                    raise TypeError(f"frames must be float32 numpy arrays, got {getattr(f, 'dtype', type(f).__name__)}")
                 m = int(f.shape[0])
                 if m > self.cap or int(f.shape[1]) != self.F:
                     raise ValueError(f"frame of shape {tuple(f.shape)} for capacity ({self.cap}, {self.F})")
@@ -148,14 +150,21 @@ class _GpuWorker:
                                                       self.threads), "pf_stage_copy")
                 pos += m
         offs[self.B] = pos
-        with torch.cuda.device(self.dev), torch.cuda.stream(self.stream):
-            s["e0"].record(self.stream)
+        with torch.cuda.device(self.dev), torch.cuda.stream(s["stream"]):
+            s["e0"].record(s["stream"])
             s["graph"].replay()
-            s["e1"].record(self.stream)
-            s["e1"].synchronize()
+            s["e1"].record(s["stream"])
+        return s, list(frame_ids), n
+
+    def finish(self, token):
+        s, frame_ids, n = token
+        s["e1"].synchronize()
         fe = s["fe"]
-        return ShardResult(self.device, list(frame_ids), fe.canvas[:n], fe.coors[:n * fe.max_voxels], fe.voxel_num[:n],
+        return ShardResult(self.device, frame_ids, fe.canvas[:n], fe.coors[:n * fe.max_voxels], fe.voxel_num[:n],
                            s["np_cnt"][:n].copy(), s["e0"].elapsed_time(s["e1"]))
+
+    def run(self, frame_ids, frames):
+        return self.finish(self.launch(frame_ids, frames))
 
     def close(self):
         for s in self.slots:
@@ -178,7 +187,7 @@ class ShardedFrontEnd:
     filled from each worker's `pillar` stand-in tensor (what bench.py's headline does: the PFN is not on the path)."""
 
     def __init__(self, config, devices=None, frames_per_device=8, max_points_per_frame=None, n_channels=64, pfn=None,
-                 depth=2, placement="spread", stage_threads=2, _worker_factory=None):
+                 depth=3, placement="spread", stage_threads=2, _worker_factory=None):
         import queue
         import threading
         if _worker_factory is None:
@@ -207,18 +216,38 @@ class ShardedFrontEnd:
             t.start()
 
     def _loop(self, i):
+        """Worker thread of GPU i.  With a two-phase worker (launch / finish) the staging copy of the next batch overlaps
+        the GPU work of the current one: a batch is finished -- its Future resolved -- only after the next one, if any is
+        queued, has been staged and enqueued."""
+        import queue
         w, q = self.workers[i], self._queues[i]
+        two_phase = hasattr(w, "launch") and hasattr(w, "finish")
+        pending = None                       # (future, token) of the batch running on the GPU
         while True:
-            job = q.get()
+            try:
+                job = q.get(block=pending is None)
+            except queue.Empty:
+                job = False                  # nothing queued right now
+            nxt = None
+            if job not in (None, False):
+                fut, ids, frames = job
+                if fut.set_running_or_notify_cancel():
+                    try:
+                        if two_phase:
+                            nxt = (fut, w.launch(ids, frames))
+                        else:
+                            fut.set_result(w.run(ids, frames))
+                    except BaseException as exc:      # hand every failure to the waiter instead of killing the worker
+                        fut.set_exception(exc)
+            if pending is not None:
+                pfut, token = pending
+                try:
+                    pfut.set_result(w.finish(token))
+                except BaseException as exc:
+                    pfut.set_exception(exc)
+            pending = nxt
             if job is None:
                 return
-            fut, ids, frames = job
-            if not fut.set_running_or_notify_cancel():
-                continue
-            try:
-                fut.set_result(w.run(ids, frames))
-            except BaseException as exc:      # hand every failure to the waiter instead of killing the worker
-                fut.set_exception(exc)
 
     def assignment(self, n_frames: int):
         """frame ids per worker for a batch of n_frames: b -> worker b mod G."""

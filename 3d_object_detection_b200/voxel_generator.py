@@ -97,9 +97,9 @@ class _FramePath:
             self.num = torch.empty((mv,), dtype=torch.int32, device=dev)
             self.vnum = torch.zeros((1,), dtype=torch.int32, device=dev)
             self.event = torch.cuda.Event()
-            self.stream = torch.cuda.Stream(dev)      # copies + graph run here; callers' streams wait on `event`
+            self.copy_event, self.copy_pending = torch.cuda.Event(), False
+            self.stream = torch.cuda.Stream(dev)      # capture stream; replays run on the caller's current stream
             self.graphs = {}                          # staged point rows (multiple of 4096) -> CUDAGraph
-            self.graph_cuda_in = None
 
     def _body(self, src_host: bool, rows: int):
         torch = _torch()
@@ -118,12 +118,14 @@ class _FramePath:
         torch = _torch()
         g = self.graphs.get(rows)
         if g is None:
+            torch.cuda.synchronize(self.dev)          # earlier replays on the caller's stream use the same buffers
             with torch.cuda.device(self.dev), torch.cuda.stream(self.stream):
                 self._body(True, rows)                # warm-up outside capture (first-use initialisation); idempotent
                 self.stream.synchronize()
                 g = torch.cuda.CUDAGraph()
                 with torch.cuda.graph(g, stream=self.stream):
                     self._body(True, rows)
+            torch.cuda.synchronize(self.dev)
             self.graphs[rows] = g
         return g
 
@@ -271,30 +273,36 @@ class VoxelGenerator:
         rows = self._stage(path, points, n)
         g = path.graph_for(rows)
         cur = torch.cuda.current_stream(path.dev)
-        with torch.cuda.stream(path.stream):
-            g.replay()
-            path.event.record(path.stream)
+        if path.copy_pending:                         # a hand-out copy of the previous call, possibly on another stream
+            cur.wait_event(path.copy_event)
+            path.copy_pending = False
+        g.replay()                                    # on the caller's current stream, like every other call
+        path.event.record(cur)
         path.event.synchronize()                      # the only wait in front of the read-back: V is data dependent
         v = int(path.np_vnum[0])
-        if device_outputs:
-            cur.wait_event(path.event)
-            with torch.cuda.device(path.dev):
-                out = (path.voxels[:v].clone(), path.coors[:v].clone(), path.num[:v].clone())
-            path.stream.wait_stream(cur)              # the next replay must not overwrite what the clones still read
+        P, mv = self.max_num_points, self.max_voxels
+        lib = path.handle.lib
+        if device_outputs:                            # fresh tensors of exactly V rows: nothing aliases the workspace
+            dev = path.dev
+            out = (torch.empty((v, P, n_feat), dtype=torch.float32, device=dev),
+                   torch.empty((v, 3), dtype=torch.int32, device=dev), torch.empty((v,), dtype=torch.int32, device=dev))
+            _lib.check(lib.pf_copy3(out[0].data_ptr(), path.voxels.data_ptr(), v * P * n_feat * 4,
+                                    out[1].data_ptr(), path.coors.data_ptr(), v * 12,
+                                    out[2].data_ptr(), path.num.data_ptr(), v * 4, cur.cuda_stream), "pf_copy3")
+            path.copy_event.record(cur)
+            path.copy_pending = True
             return out, v
         if self._pool and self._pool_F != n_feat:
             self._pool = []
         self._pool_F = n_feat
         blk = self._out_block()
-        with torch.cuda.stream(path.stream):
-            if blk is not None:                       # D2H of exactly V rows, straight into the arrays handed out
-                blk.tv[:v].copy_(path.voxels[:v], non_blocking=True)
-                blk.tc[:v].copy_(path.coors[:v], non_blocking=True)
-                blk.tn[:v].copy_(path.num[:v], non_blocking=True)
-                path.stream.synchronize()
-                return (blk.nv[:v], blk.nc[:v], blk.nn[:v]), v
-            out = (path.voxels[:v].cpu().numpy(), path.coors[:v].cpu().numpy(), path.num[:v].cpu().numpy())
-        return out, v
+        if blk is not None:                           # D2H of exactly V rows, straight into the arrays handed out
+            _lib.check(lib.pf_copy3(blk.tv.data_ptr(), path.voxels.data_ptr(), v * P * n_feat * 4,
+                                    blk.tc.data_ptr(), path.coors.data_ptr(), v * 12,
+                                    blk.tn.data_ptr(), path.num.data_ptr(), v * 4, cur.cuda_stream), "pf_copy3")
+            cur.synchronize()
+            return (blk.nv[:v], blk.nc[:v], blk.nn[:v]), v
+        return (path.voxels[:v].cpu().numpy(), path.coors[:v].cpu().numpy(), path.num[:v].cpu().numpy()), v
 
     # ------------------------------------------------------------------------------------------------
     def _run(self, frames_dev, compact: bool, coors_stride: int):

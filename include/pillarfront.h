@@ -90,6 +90,12 @@ PF_API size_t pf_workspace_bytes(const pf_handle *h);
  * driver's synchronous staged copy.  Pure host code; touches no CUDA state. */
 PF_API int pf_stage_copy(void *dst, const void *src, size_t bytes, int threads);
 
+/* Up to three asynchronous copies (direction inferred from the pointers: device -> device, or device -> PINNED host) on
+ * `stream` in one call: how VoxelGenerator.generate hands out exactly V rows of voxels / coors / num_points after it has
+ * read the voxel count (one library call instead of three framework copies).  A zero size skips that copy. */
+PF_API int pf_copy3(void *dst0, const void *src0, size_t bytes0, void *dst1, const void *src1, size_t bytes1,
+                    void *dst2, const void *src2, size_t bytes2, void *stream);
+
 /* Diagnostics: with timing enabled every voxelise / fill call of this handle records a CUDA event after each of
  * its kernels (eager launches only -- do not capture such a call into a graph).  pf_debug_stage_times waits for
  * the last call and writes the 8 stage durations in milliseconds (quantize, assign, tile_rank, column_scan, slot,
@@ -99,7 +105,8 @@ PF_API int pf_debug_stage_timing(pf_handle *h, int enable);
  * PF_FILL_VARIANT read at first use).  0 = one warp per 128 cells, 16-byte streaming stores; 1 = one warp per 256
  * cells, 32-byte streaming stores (STG.256, the default); 2 = TMA bulk stores of shared-memory tiles (cp.async.bulk,
  * UBLKCP), 512 bytes per copy; 3 = as 2 with an L2 evict-first hint; 4 / 5 = as 2 / 3 with 2 KB per copy; 6 = one warp
- * per 512 cells, two 32-byte stores per lane and channel; -1 = the library default.  Every variant writes the same bytes.  Returns the
+ * per 512 cells, two 32-byte stores per lane and channel; -1 = the library default: 6 for canvases of at least 2^25 cells
+ * (batch * nx * ny), else 1.  Every variant writes the same bytes.  Returns the
  * variant now in force, or a negative pf_status. */
 PF_API int pf_debug_set_fill_variant(int variant);
 PF_API int pf_debug_stage_times(pf_handle *h, float *ms, int capacity);
@@ -160,7 +167,10 @@ PF_API int pf_pfn(const float *voxels, const int32_t *num_points, const int32_t 
            const float *pfn_weight, const float *pfn_scale, const float *pfn_shift, int n_ch,
            float *pillar_feats, void *stream);
 
-/* Stand-alone decoration of already voxelised pillars (host-known row count). */
+/* Stand-alone decoration of already voxelised pillars (host-known row count).  max_points 1..4096 and num_features
+ * 3..16 as long as one CTA's pillars fit the device's opt-in shared memory (about 8 * max_points * (2 * num_features + 5)
+ * * 4 bytes outside the F = 4 fast path; e.g. F = 16 allows max_points <= ~190 on B200); PF_ERR_UNSUPPORTED otherwise.
+ * pf_create applies the same rule to (desc.max_points, desc.num_features). */
 PF_API int pf_decorate(const float *voxels, const int32_t *num_points, const int32_t *coors, int coors_stride,
                 int64_t n_voxels, int max_points, int num_features,
                 float vx, float vy, float x_off, float y_off, float *features, void *stream);

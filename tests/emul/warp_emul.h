@@ -83,6 +83,15 @@ static inline unsigned __dp4a(unsigned a, unsigned b, unsigned c)
     for (int k = 0; k < 4; ++k) c += ((a >> (8 * k)) & 0xffu) * ((b >> (8 * k)) & 0xffu);
     return c;
 }
+static inline unsigned __vaddus4(unsigned a, unsigned b)
+{
+    unsigned r = 0;
+    for (int k = 0; k < 4; ++k) {
+        unsigned s = ((a >> (8 * k)) & 0xffu) + ((b >> (8 * k)) & 0xffu);
+        r |= (s > 255u ? 255u : s) << (8 * k);
+    }
+    return r;
+}
 static inline float __fsub_rn(float a, float b) { return a - b; }       // compiled with -ffp-contract=off
 static inline float __fdiv_rn(float a, float b) { return a / b; }
 static inline float __int_as_float(int v)

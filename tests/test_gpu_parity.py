@@ -189,6 +189,31 @@ def test_voxelize_rejects_bad_input(pfm):
     vg.close()
 
 
+def test_oversized_shapes_are_refused_not_crashed(pfm):
+    """(max_points, features) whose gather / decoration kernel cannot fit a CTA's shared memory are refused at
+    validation time with PF_ERR_UNSUPPORTED, not with a raw CUDA launch error; shapes inside the limit still work."""
+    big_v = torch.zeros((3, 4096, 4), device="cuda")
+    n = torch.ones((3,), dtype=torch.int32, device="cuda")
+    c = torch.zeros((3, 3), dtype=torch.int32, device="cuda")
+    with pytest.raises(pfm.PillarFrontError, match="shared memory"):
+        pfm.decorate(big_v, n, c, 0.2, 0.2, 0.1, 0.1)
+    cfg = dict(detection_range=[0.0, 0.0, 0.0, 8.0, 8.0, 1.0], voxel_size=[1.0, 1.0, 1.0], max_voxels=10,
+               max_num_points=255, num_point_features=16, batch_size=1, device=0)
+    vg = pfm.VoxelGenerator(dict(cfg))
+    with pytest.raises(pfm.PillarFrontError, match="shared memory"):
+        vg.generate(np.zeros((5, 16), np.float32))
+    vg.close()
+    cfg["max_num_points"] = 120                      # 8 * 120 * 37 * 4 bytes = 142 KB: fits
+    geom = cfgmod.derive_grid(dict(cfg))
+    pts = np.random.default_rng(1).random((500, 16), dtype=np.float32) * 8
+    vg = pfm.VoxelGenerator(dict(cfg))
+    util.assert_vox_equal(vg.generate(pts), oracle.generate(geom, pts, 10, 120), "P=120 F=16")
+    vg.close()
+    ok_v = torch.rand((5, 600, 4), device="cuda")   # F = 4, P > 512 -> generic kernel, 8 * 600 * 13 * 4 = 250 KB: refused
+    with pytest.raises(pfm.PillarFrontError, match="shared memory"):
+        pfm.decorate(ok_v, torch.full((5,), 600, dtype=torch.int32, device="cuda"), torch.zeros((5, 3), dtype=torch.int32, device="cuda"), 0.2, 0.2, 0.1, 0.1)
+
+
 # ------------------------------------------------------------------------------------------------ decorate
 @pytest.mark.parametrize("gkey", util.GRID_KEYS)
 @pytest.mark.parametrize("name", ["s1", "s2_ring", "s4_edges", "dense_cap", "n5"])
