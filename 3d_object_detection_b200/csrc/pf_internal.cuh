@@ -193,9 +193,19 @@ __device__ __forceinline__ void st_cs_f4(float *ptr, float a, float b, float c, 
 }
 #endif
 
-// flag / status words other CTAs poll or publish (always through L2, never a cached copy)
+// flag / status words other CTAs poll or publish, and single words several threads may write or read concurrently BY
+// DESIGN (always through L2, never a cached copy; a 32-bit access is indivisible on the device).  The host emulation
+// states the same thing to ThreadSanitizer with relaxed atomics.
+#ifdef PF_HOST_EMUL
+__device__ __forceinline__ int ld_flag(const int32_t *p) { return __atomic_load_n(p, __ATOMIC_RELAXED); }
+__device__ __forceinline__ void st_flag(int32_t *p, int v) { __atomic_store_n(p, v, __ATOMIC_RELAXED); }
+__device__ __forceinline__ void st_same(int32_t *p, int v) { __atomic_store_n(p, v, __ATOMIC_RELAXED); }
+#else
+// a word several threads store the SAME value to (plain store on the device)
+__device__ __forceinline__ void st_same(int32_t *p, int v) { *p = v; }
 __device__ __forceinline__ int ld_flag(const int32_t *p) { return *reinterpret_cast<const volatile int32_t *>(p); }
 __device__ __forceinline__ void st_flag(int32_t *p, int v) { *reinterpret_cast<volatile int32_t *>(p) = v; }
+#endif
 
 #endif  // __CUDACC__ || PF_HOST_EMUL
 

@@ -77,7 +77,7 @@ __global__ void __launch_bounds__(256) k_quantize(Params p, Work w, const float 
         const int i = i0 + k * 256;
         c[k] = cell_of_point(x[k], y[k], z[k], p);
         if (i < n) w.cellid[(size_t)f * p.npts_cap + i] = c[k];
-        seen[k] = c[k] >= 0 ? __ldcg(grid + c[k]) : -1;
+        seen[k] = c[k] >= 0 ? __ldcg(grid + c[k]) : -1;   // races with other points' atomicMin by design (see above)
     }
 #pragma unroll
     for (int k = 0; k < kQPer; ++k) {
@@ -306,67 +306,11 @@ __global__ void __launch_bounds__(kTileWarps * 32) k_tile_rank(Params p, Work w,
 
 // ---------------------------------------------------------------------------------------------------------
 // K5: saturating exclusive scan down every voxel column of the count matrix (in place), totals -> vcount.
-// A warp owns 32 adjacent 4-column words (128 voxels); the S warps of a CTA split the rows (tiles) of those columns into
-// S slices of <= 16 rows, so every thread issues ALL its loads at once (one L2 round trip instead of rows / 16 of them --
-// the round-1 kernel, one thread per word walking all rows, was latency-bound at 10 us for 7.5 MB), reduces its slice with
-// per-byte saturating adds, and picks its starting value from the slice totals of the warps in front of it.
-constexpr int kScanRows = 16;
-
-__global__ void __launch_bounds__(512) k_column_scan(Params p, Work w, const int32_t *__restrict__ frame_offsets,
-                                                      int max_frame_points)
-{
-    __shared__ uint32_t s_part[16][33];
-    const int f = blockIdx.y;
-    int n = frame_offsets[f + 1] - frame_offsets[f];
-    if (n > max_frame_points) n = max_frame_points;
-    const int n_tiles = (n + kTile - 1) / kTile;
-    const int n_vox = w.vnum[f];
-    const int lane = threadIdx.x & 31, slice = threadIdx.x >> 5, n_slices = blockDim.x >> 5;
-    const int col = (blockIdx.x * 32 + lane) * 4;
-    if (blockIdx.x * 128 >= n_vox) return;            // block-uniform
-    const bool active = col < n_vox;
-    uint32_t *m = reinterpret_cast<uint32_t *>(w.cnt + (size_t)f * p.tiles_cap * p.vcols + col);
-    const size_t row_words = p.vcols / 4;
-    const int rows = (n_tiles + n_slices - 1) / n_slices;     // <= kScanRows: the launcher sizes n_slices for it
-    const int t0 = slice * rows;
-    const int t1 = (t0 + rows) < n_tiles ? (t0 + rows) : n_tiles;
-    uint32_t v[kScanRows];
-#pragma unroll
-    for (int u = 0; u < kScanRows; ++u) v[u] = (active && t0 + u < t1) ? m[(size_t)(t0 + u) * row_words] : 0u;
-    uint32_t tot = 0;
-#pragma unroll
-    for (int u = 0; u < kScanRows; ++u) tot = __vaddus4(tot, v[u]);      // per-byte saturating add: caps at kCountCap = 255
-    s_part[slice][lane] = tot;
-    __syncthreads();
-    uint32_t run = 0;
-    for (int s = 0; s < slice; ++s) run = __vaddus4(run, s_part[s][lane]);
-    if (!active) return;
-#pragma unroll
-    for (int u = 0; u < kScanRows; ++u) {
-        if (t0 + u < t1) {
-            m[(size_t)(t0 + u) * row_words] = run;
-            run = __vaddus4(run, v[u]);
-        }
-    }
-    if (slice == n_slices - 1) {
-#pragma unroll
-        for (int k = 0; k < 4; ++k) {
-            const int c = (int)((run >> (8 * k)) & 0xffu);
-            if (col + k < n_vox) w.vcount[(size_t)f * p.max_voxels + col + k] = c < p.P ? c : p.P;
-        }
-    }
-}
-
-// the launch shape of k_column_scan for frames of up to `tiles` tiles: warps (= row slices) per CTA, or 0 when a frame
-// is too long for <= kScanRows rows per slice with 16 slices (> 524 288 points): the caller falls back to the serial kernel
-inline int column_scan_slices(int tiles)
-{
-    const int s = (tiles + kScanRows - 1) / kScanRows;
-    return s < 1 ? 1 : (s > 16 ? 0 : s);
-}
-
-// one thread per 4-column word walking all rows, 16 loads in flight: any frame length
-__global__ void __launch_bounds__(128) k_column_scan_serial(Params p, Work w, const int32_t *__restrict__ frame_offsets,
+// A thread owns 4 adjacent columns (one 32-bit word per row) and walks all rows with 16 independent loads in flight;
+// per-byte saturating adds (__vaddus4) cap every counter at kCountCap = 255.  (Round 2 also tried splitting the rows of
+// a column over the warps of a CTA so that every thread issues all its loads at once: same 10 us at 20 cm x 8, 61 instead
+// of 38 us at 10 cm x 32 -- profiles/r2_chain_experiments.md E3.)
+__global__ void __launch_bounds__(128) k_column_scan(Params p, Work w, const int32_t *__restrict__ frame_offsets,
                                                             int max_frame_points)
 {
     const int f = blockIdx.y;
@@ -422,7 +366,7 @@ __global__ void __launch_bounds__(256) k_slot(Params p, Work w, const int32_t *_
         for (int k = 0; k < kQPer; ++k) {
             const int i = i0 + k * 256;
             const int c = i < n ? w.cellid[(size_t)f * p.npts_cap + i] : -1;
-            if (c >= 0) w.grid[(size_t)f * p.cells + c] = kEmpty;
+            if (c >= 0) st_same(w.grid + (size_t)f * p.cells + c, kEmpty);   // every point of the cell stores the same word
         }
     }
 #pragma unroll

@@ -243,10 +243,7 @@ cudaError_t launch_voxelize(const Params &p, const Work &w, const VoxelizeArgs &
     }
     k_tile_rank<<<g_tiles, kTileWarps * 32, p.vcols, stream>>>(p, w, a.frame_offsets, npts);
     mark(w, kEvTileRank, stream);
-    if (const int slices = column_scan_slices(tiles))
-        k_column_scan<<<dim3((p.vcols / 4 + 31) / 32, B), 32 * slices, 0, stream>>>(p, w, a.frame_offsets, npts);
-    else
-        k_column_scan_serial<<<dim3((p.vcols / 4 + 127) / 128, B), 128, 0, stream>>>(p, w, a.frame_offsets, npts);
+    k_column_scan<<<dim3((p.vcols / 4 + 127) / 128, B), 128, 0, stream>>>(p, w, a.frame_offsets, npts);
     mark(w, kEvColumnScan, stream);
     k_slot<<<g_pts, 256, 0, stream>>>(p, w, a.frame_offsets, npts, a.keep_cell_map ? 0 : 1);
     mark(w, kEvSlot, stream);

@@ -72,8 +72,7 @@ void emul_vox_destroy(void *hv) { delete static_cast<EmulHandle *>(hv); }
 int emul_voxelize(void *hv, const float *points, const int *frame_offsets, int n_frames, int max_frame_points,
                   int point_stride, int keep_cell_map, float *voxels, int *coors, int *num_points, int *voxel_num)
 {
-    const bool serial_scan = keep_cell_map >= 2;      // test hook: the fall-back column scan of very long frames
-    keep_cell_map &= 1;
+
     EmulHandle *h = static_cast<EmulHandle *>(hv);
     const Params p = h->p;
     const Work w = h->w;
@@ -92,12 +91,8 @@ int emul_voxelize(void *hv, const float *points, const int *frame_offsets, int n
                    [=] { k_assign(p, w, frame_offsets, voxel_num, npts); });
     pf_emul_launch(dim3((unsigned)tiles, (unsigned)B), kTileWarps * 32, (size_t)p.vcols,
                    [=] { k_tile_rank(p, w, frame_offsets, npts); });
-    if (const int slices = serial_scan ? 0 : column_scan_slices(tiles))
-        pf_emul_launch(dim3((unsigned)((p.vcols / 4 + 31) / 32), (unsigned)B), 32 * slices, 0,
-                       [=] { k_column_scan(p, w, frame_offsets, npts); });
-    else
-        pf_emul_launch(dim3((unsigned)((p.vcols / 4 + 127) / 128), (unsigned)B), 128, 0,
-                       [=] { k_column_scan_serial(p, w, frame_offsets, npts); });
+    pf_emul_launch(dim3((unsigned)((p.vcols / 4 + 127) / 128), (unsigned)B), 128, 0,
+                   [=] { k_column_scan(p, w, frame_offsets, npts); });
     pf_emul_launch(dim3((unsigned)((npts + kPtsPerCta - 1) / kPtsPerCta), (unsigned)B), 256, 0,
                    [=] { k_slot(p, w, frame_offsets, npts, keep_cell_map ? 0 : 1); });
     // host gather (what k_gather4 / k_gather do with the slot lists)

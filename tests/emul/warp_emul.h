@@ -103,7 +103,7 @@ static inline float __int_as_float(int v)
 template <class T>
 static inline T __ldg(const T *p) { return *p; }
 template <class T>
-static inline T __ldcg(const T *p) { return *reinterpret_cast<const volatile T *>(p); }
+static inline T __ldcg(const T *p) { return __atomic_load_n(p, __ATOMIC_RELAXED); }   // one indivisible L2 load on the device
 static inline uint4 __ldcg(const uint4 *p) { return *p; }
 static inline int atomicMin(int *p, int v)
 {

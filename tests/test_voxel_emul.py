@@ -38,7 +38,7 @@ class Emul:
         self.h = L.emul_vox_create(off.ctypes.data_as(fp), vs.ctypes.data_as(fp), gs.ctypes.data_as(ip), max_voxels, P, F,
                                    max_frames, cap)
 
-    def run(self, frames, max_frame_points=None, keep=False, serial_scan=False):
+    def run(self, frames, max_frame_points=None, keep=False):
         fp, ip = C.POINTER(C.c_float), C.POINTER(C.c_int)
         B = len(frames)
         sizes = [len(f) for f in frames]
@@ -49,7 +49,7 @@ class Emul:
         num = np.full((B * self.mv,), -7, np.int32)
         vnum = np.full((B,), -7, np.int32)
         mfp = max(sizes + [1]) if max_frame_points is None else max_frame_points
-        rc = self.L.emul_voxelize(self.h, pts.ctypes.data_as(fp), offs.ctypes.data_as(ip), B, mfp, self.F, (1 if keep else 0) | (2 if serial_scan else 0),
+        rc = self.L.emul_voxelize(self.h, pts.ctypes.data_as(fp), offs.ctypes.data_as(ip), B, mfp, self.F, 1 if keep else 0,
                                   vox.ctypes.data_as(fp), coors.ctypes.data_as(ip), num.ctypes.data_as(ip),
                                   vnum.ctypes.data_as(ip))
         assert rc == 0, f"workspace invariant broken after the call (code {rc})"
@@ -86,9 +86,9 @@ def test_emulated_chain_matches_oracle(emul, gkey, mv, P):
     em = Emul(emul, geom, mv, P, 4, len(frames), max(len(f) for f in frames))
     refs = [oracle.generate(geom, f, mv, P) for f in frames]
     assert any(len(r[2]) == mv for r in refs) and any(0 < len(r[2]) < mv for r in refs)
-    for rep in range(3):                              # third call: the fall-back column scan of very long frames
-        got = em.run(frames if rep != 1 else frames[::-1], serial_scan=rep == 2)
-        for f, (g, r) in enumerate(zip(got, refs if rep != 1 else refs[::-1])):
+    for rep in range(2):
+        got = em.run(frames if rep == 0 else frames[::-1])
+        for f, (g, r) in enumerate(zip(got, refs if rep == 0 else refs[::-1])):
             _same(g, r, f"{gkey} rep {rep} frame {f}")
     em.close()
 
@@ -142,9 +142,9 @@ def test_emulated_overlong_frame_is_truncated(emul):
     em.close()
 
 
-def test_emulated_column_scan_row_slices(emul):
-    """More than 16 tiles per frame: the column scan splits the rows over two warps (slice totals through shared
-    memory); a voxel whose points are spread over all 17 tiles exercises the carry between the slices."""
+def test_emulated_many_tiles_per_frame(emul):
+    """17 tiles per frame: a voxel whose points are spread over every tile (carry down the whole column of the count
+    matrix), with saturating P = 255 and with an overflowing max_voxels."""
     cfg = cfgmod.builtin_config("20cm")
     geom = cfgmod.derive_grid(cfg)
     f = synth.make_frame("S1", geom, 34000, 3, 40)           # 40 cells, ~800 points each, in every tile
