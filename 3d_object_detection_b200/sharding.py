@@ -74,7 +74,7 @@ class ShardResult:
 class _GpuWorker:
     """One GPU: `depth` PillarFrontEnd replicas (workspace, outputs, pinned staging, one stream and one CUDA graph
     each), used in turn; the graph holds H2D of the staged frames + offsets, voxelise + decorate (+ fused PFN), canvas
-    fill, D2H of the voxel counts."""
+    fill, D2H of the voxel counts; the points themselves are copied in front of it, one copy per frame."""
 
     def __init__(self, config, device, frames_per_device, max_points_per_frame, n_channels, pfn, depth, stage_threads):
         import copy
@@ -115,7 +115,7 @@ class _GpuWorker:
         self.turn = 0
 
     def _body(self, s):
-        s["d_pts"].copy_(s["h_pts"], non_blocking=True)
+        # the points are copied in front of the graph, frame by frame, from wherever they live (launch())
         s["d_offs"].copy_(s["h_offs"], non_blocking=True)
         if self.pfn is not None:
             s["fe"].step(s["d_pts"], s["d_offs"], pfn=self.pfn)
@@ -124,8 +124,13 @@ class _GpuWorker:
         s["h_cnt"].copy_(s["fe"].voxel_num, non_blocking=True)
 
     def launch(self, frame_ids, frames):
-        """Stage `frames` (list of (N, F) float32 arrays, at most B of them) into the next slot's pinned buffer and
-        enqueue that slot's graph; returns a token for :meth:`finish`.  Does not wait for the GPU."""
+        """Move `frames` (at most B arrays of shape (N, F), float32) onto the GPU and enqueue the next slot's graph;
+        returns a token for :meth:`finish`.  Does not wait for the GPU.  A frame may be
+          * a numpy array (pageable host memory, what a dataset hands over): copied into the slot's pinned staging
+            buffer by pf_stage_copy, then one asynchronous H2D;
+          * a pinned torch CPU tensor: one asynchronous H2D straight from it, no staging copy (the caller must not
+            rewrite it before the batch has finished);
+          * a CUDA tensor on this GPU: a device-to-device copy."""
         torch = self.torch
         s = self.slots[self.turn % len(self.slots)]
         self.turn += 1
@@ -135,23 +140,30 @@ class _GpuWorker:
         lib = self._lib.load()
         offs = s["np_offs"]
         pos = 0
-        for b in range(self.B):
-            offs[b] = pos
-            if b < n:
-                f = frames[b]
-                if str(getattr(f, "dtype", None)) != "float32":
-                    raise TypeError(f"frames must be float32 numpy arrays, got {getattr(f, 'dtype', type(f).__name__)}")
-                m = int(f.shape[0])
-                if m > self.cap or int(f.shape[1]) != self.F:
-                    raise ValueError(f"frame of shape {tuple(f.shape)} for capacity ({self.cap}, {self.F})")
-                if m:
-                    src = f if f.flags.c_contiguous else f.copy()
-                    self._lib.check(lib.pf_stage_copy(s["np_pts"][pos:].ctypes.data, src.ctypes.data, src.nbytes,
-                                                      self.threads), "pf_stage_copy")
-                pos += m
-        offs[self.B] = pos
         with torch.cuda.device(self.dev), torch.cuda.stream(s["stream"]):
             s["e0"].record(s["stream"])
+            for b in range(self.B):
+                offs[b] = pos
+                if b >= n:
+                    continue
+                f = frames[b]
+                is_t = torch.is_tensor(f)
+                if (f.dtype != torch.float32) if is_t else (str(getattr(f, "dtype", None)) != "float32"):
+                    raise TypeError(f"frames must be float32, got {getattr(f, 'dtype', type(f).__name__)}")
+                m = int(f.shape[0])
+                if f.ndim != 2 or m > self.cap or int(f.shape[1]) != self.F:
+                    raise ValueError(f"frame of shape {tuple(f.shape)} for capacity ({self.cap}, {self.F})")
+                if m:
+                    dst = s["d_pts"][pos:pos + m]
+                    if is_t:
+                        dst.copy_(f.contiguous(), non_blocking=True)
+                    else:
+                        src = f if f.flags.c_contiguous else f.copy()
+                        self._lib.check(lib.pf_stage_copy(s["np_pts"][pos:].ctypes.data, src.ctypes.data, src.nbytes,
+                                                          self.threads), "pf_stage_copy")
+                        dst.copy_(s["h_pts"][pos:pos + m], non_blocking=True)
+                pos += m
+            offs[self.B] = pos
             s["graph"].replay()
             s["e1"].record(s["stream"])
         return s, list(frame_ids), n

@@ -60,6 +60,8 @@ def parse_args():
     ap.add_argument("--pipelines", type=int, default=3, help="e2e: independent stream/workspace sets in flight")
     ap.add_argument("--min-seconds", type=float, default=0.0,
                     help="raise --steps until the timed region lasts at least this long (BASELINE configs[4]: >= 2 s)")
+    ap.add_argument("--pinned-frames", action="store_true",
+                    help="--sharded: hand the frames over as pinned torch tensors (no host staging copy) instead of pageable numpy")
     ap.add_argument("--sharded", action="store_true",
                     help="single-process mode: ONE process drives --gpus N GPUs through the package's ShardedFrontEnd "
                          "(one worker thread per GPU, numpy frames in, frame b -> GPU b mod N) instead of one rank per GPU")
@@ -614,6 +616,9 @@ def run_sharded(args):
     per_dev = [make_batch(pfm, cfg, geom, B, r)[0] for r in range(G)]
     frames = [per_dev[b % G][b // G] for b in range(G * B)]          # frame b lands on worker b mod G
     n_points = sum(len(f) for f in frames)
+    nbytes = sum(f.nbytes for f in frames)
+    if args.pinned_frames:
+        frames = [torch.from_numpy(f).pin_memory() for f in frames]
     K, W = args.steps, max(args.warmup, 3)
     with pfm.ShardedFrontEnd(cfg, devices=G, frames_per_device=B, max_points_per_frame=cfg["frame_points"], depth=3,
                              stage_threads=max(1, min(4, (os.cpu_count() or 1) // max(G, 1)))) as sfe:
@@ -640,8 +645,9 @@ def run_sharded(args):
                                    "busiest-GPU sum of CUDA-event graph times per step is below",
                        "max_worker_graph_ms_per_step": 1e3 * dev_s / K},
             "e2e": {"value": n_points * K / wall, "unit": UNIT, "frames_per_s": G * B * K / wall, "ms_per_step": 1e3 * wall / K,
-                    "h2d_bytes_per_step": int(sum(f.nbytes for f in frames) // G), "d2h_bytes_per_step": 4 * B,
-                    "api": "ShardedFrontEnd.submit(list of pageable numpy frames): host staging copy into pinned memory, H2D, "
+                    "h2d_bytes_per_step": int(nbytes // G), "d2h_bytes_per_step": 4 * B,
+                    "frames": "pinned torch tensors (no staging copy)" if args.pinned_frames else "pageable numpy arrays (staged into pinned memory by pf_stage_copy)",
+                    "api": "ShardedFrontEnd.submit(list of host frames): [host staging copy into pinned memory,] one H2D per frame, "
                            "voxelise + decorate + canvas fill, D2H of the voxel counts; host wall clock over all K steps"},
             "gpu_launches": K * G * (pfm.PillarFrontEnd.n_kernels_voxelize(cfg["frame_points"]) + 1),
             "clocks": clocks}

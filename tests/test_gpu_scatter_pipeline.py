@@ -398,7 +398,7 @@ def test_sharded_front_end_matches_oracle(pf):
                 s["pillar"].copy_(torch.randn(s["pillar"].shape, generator=torch.Generator().manual_seed(w.device)).to(s["pillar"].device))
             stand_in.append(w.slots[0]["pillar"].cpu().numpy())
         first = sfe.submit(frames)
-        second = sfe.submit(frames[::-1])
+        second = sfe.submit([torch.from_numpy(f).pin_memory() for f in frames[::-1]])      # pinned tensors: no staging copy
         for order, futs in ((frames, first), (frames[::-1], second)):
             for wi, fut in enumerate(futs):
                 r = fut.result()

@@ -15,7 +15,8 @@ for n in 8 4 2; do
   timeout 300 $R bench.py --gpus $n --steps 100 $S > $o/${tag}_scale_20cm_n$n.json 2> $o/${tag}_scale_20cm_n$n.err
 done
 timeout 300 python bench.py --sharded --gpus 8 --steps 100 > $o/${tag}_sharded_n8.json 2> $o/${tag}_sharded_n8.err
-timeout 300 python bench.py --sharded --gpus 2 --steps 100 > $o/${tag}_sharded_n2.json 2> $o/${tag}_sharded_n2.err
+timeout 300 python bench.py --sharded --pinned-frames --gpus 8 --steps 100 > $o/${tag}_sharded_pinned_n8.json 2> $o/${tag}_sharded_pinned_n8.err
+timeout 300 python bench.py --sharded --pinned-frames --gpus 1 --steps 100 > $o/${tag}_sharded_pinned_n1.json 2> $o/${tag}_sharded_pinned_n1.err
 R="python -m torch.distributed.run --nnodes=1 --nproc-per-node 8 --master-addr 127.0.0.1 --master-port 29790"
 timeout 400 $R bench.py --gpus 8 --grid nuscene --batch 8 --min-seconds 2 $S > $o/${tag}_cfg3_nuscene_b8_n8.json 2> $o/${tag}_cfg3.err
 timeout 400 $R bench.py --gpus 8 --grid 20cm --batch 64 --min-seconds 2 $S > $o/${tag}_cfg4_20cm_b64_n8.json 2> $o/${tag}_cfg4.err
