@@ -12,7 +12,7 @@ LIB_PATH = Path(__file__).resolve().parent / "lib" / "libpillarfront.so"
 EXPORTS = ["pf_version", "pf_last_error_string", "pf_create", "pf_destroy", "pf_workspace_bytes",
            "pf_voxelize", "pf_voxelize_decorate", "pf_voxelize_pfn", "pf_pfn", "pf_decorate", "pf_scatter", "pf_scatter_from_map",
            "pf_scatter_backward", "pf_anchor_mask", "pf_nms", "pf_nms_scratch_bytes",
-           "pf_debug_stage_timing", "pf_debug_stage_times", "pf_debug_set_fill_variant", "pf_discard_cell_map", "pf_stage_copy", "pf_copy3",
+           "pf_debug_stage_timing", "pf_debug_stage_times", "pf_debug_set_fill_variant", "pf_discard_cell_map", "pf_stage_copy", "pf_copy3", "pf_upload_frames",
            "pf_postprocess", "pf_post_scratch_bytes", "pf_post_scratch_layout"]
 
 
@@ -98,6 +98,9 @@ def load():
     L.pf_debug_stage_times.argtypes = [_p, C.POINTER(C.c_float), C.c_int]
     L.pf_stage_copy.restype = C.c_int
     L.pf_stage_copy.argtypes = [_p, _p, C.c_size_t, C.c_int]
+    L.pf_upload_frames.restype = C.c_int
+    L.pf_upload_frames.argtypes = [_p, _p, C.POINTER(_p), C.POINTER(C.c_int64), C.POINTER(C.c_int32), C.c_int, C.c_int, C.c_int,
+                                   C.c_int, _p, _p]
     L.pf_copy3.restype = C.c_int
     L.pf_copy3.argtypes = [_p, _p, C.c_size_t, _p, _p, C.c_size_t, _p, _p, C.c_size_t, _p]
     L.pf_debug_set_fill_variant.restype = C.c_int

@@ -243,9 +243,41 @@ int pf_copy3(void *dst0, const void *src0, size_t bytes0, void *dst1, const void
     return PF_OK;
 }
 
+int pf_upload_frames(void *device_points, void *pinned_stage, const void *const *frames, const int64_t *rows,
+                     const int32_t *kinds, int n_frames, int n_slots, int row_bytes, int threads, int32_t *pinned_offsets,
+                     void *stream)
+{
+    if (n_frames < 0 || n_slots < n_frames || row_bytes < 1) return fail(PF_ERR_INVALID_ARGUMENT, "pf_upload_frames: bad sizes");
+    if (!device_points || !pinned_offsets || (n_frames > 0 && (!frames || !rows || !kinds)))
+        return fail(PF_ERR_INVALID_ARGUMENT, "pf_upload_frames: null argument");
+    Range nvtx_range("pf_upload_frames");
+    cudaStream_t st = static_cast<cudaStream_t>(stream);
+    int64_t pos = 0;
+    for (int b = 0; b < n_slots; ++b) {
+        if (pos > 0x7fffffff) return fail(PF_ERR_CAPACITY, "pf_upload_frames: more than 2^31 points");
+        pinned_offsets[b] = (int32_t)pos;
+        if (b >= n_frames || rows[b] <= 0) continue;
+        const size_t bytes = (size_t)rows[b] * row_bytes;
+        char *dst = static_cast<char *>(device_points) + (size_t)pos * row_bytes;
+        const void *src = frames[b];
+        if (kinds[b] == 0) {                    // pageable host memory: through the pinned staging buffer
+            if (!pinned_stage) return fail(PF_ERR_INVALID_ARGUMENT, "pf_upload_frames: pageable frame without a staging buffer");
+            char *stage = static_cast<char *>(pinned_stage) + (size_t)pos * row_bytes;
+            pf_stage_copy(stage, src, bytes, threads);
+            src = stage;
+        }
+        cudaError_t e = cudaMemcpyAsync(dst, src, bytes, cudaMemcpyDefault, st);
+        if (e != cudaSuccess) return cuda_fail(e, "pf_upload_frames");
+        pos += rows[b];
+    }
+    if (pos > 0x7fffffff) return fail(PF_ERR_CAPACITY, "pf_upload_frames: more than 2^31 points");
+    pinned_offsets[n_slots] = (int32_t)pos;
+    return PF_OK;
+}
+
 int pf_debug_set_fill_variant(int variant)
 {
-    if (variant < -1 || variant > 6) return fail(PF_ERR_INVALID_ARGUMENT, "pf_debug_set_fill_variant: variant %d outside -1..6", variant);
+    if (variant < -1 || variant > 8) return fail(PF_ERR_INVALID_ARGUMENT, "pf_debug_set_fill_variant: variant %d outside -1..8", variant);
     pf::set_fill_variant(variant);
     return pf::fill_variant();
 }

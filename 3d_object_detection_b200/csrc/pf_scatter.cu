@@ -51,8 +51,8 @@ __device__ __forceinline__ void st_cs_f8(float *ptr, const float (&v)[8])
 
 // CPL = cells per lane: 4 -> a warp owns 128 cells and stores 16 bytes per lane and channel (STG.128),
 //                       8 -> a warp owns 256 cells and stores 32 bytes per lane and channel (STG.256).
-template <int MODE, bool FEAT4, int CPL, int WARPS = kFillWarps, int STAGE = kFillStage>
-__global__ void __launch_bounds__(WARPS * 32) k_canvas_fill(int32_t *__restrict__ map, const float *__restrict__ feats,
+template <int MODE, bool FEAT4, int CPL, int WARPS = kFillWarps, int STAGE = kFillStage, int MINB = 1>
+__global__ void __launch_bounds__(WARPS * 32, MINB) k_canvas_fill(int32_t *__restrict__ map, const float *__restrict__ feats,
                                                                  long long sv, long long sc,
                                                                  const int32_t *__restrict__ vnum, int max_voxels,
                                                                  int compact, int batch, int n_ch, int plane,
@@ -393,12 +393,12 @@ int fill_variant()
 {
     if (!g_fill_set) {
         const char *e = getenv("PF_FILL_VARIANT");
-        g_fill_variant = (e && e[0] >= '0' && e[0] <= '6') ? e[0] - '0' : kFillDefault;
+        g_fill_variant = (e && e[0] >= '0' && e[0] <= '8') ? e[0] - '0' : kFillDefault;
         g_fill_set = true;
     }
     return g_fill_variant;
 }
-void set_fill_variant(int v) { g_fill_variant = (v >= 0 && v <= 6) ? v : kFillDefault, g_fill_set = true; }
+void set_fill_variant(int v) { g_fill_variant = (v >= 0 && v <= 8) ? v : kFillDefault, g_fill_set = true; }
 
 template <int MODE>
 static cudaError_t run_fill(int32_t *map, const float *feats, int64_t sv, int64_t sc, const int32_t *vnum,
@@ -450,6 +450,20 @@ static cudaError_t run_fill(int32_t *map, const float *feats, int64_t sv, int64_
             k_canvas_fill<MODE, true, 16, 4, 2304><<<blocks6, 128, 0, stream>>>(map, feats, sv, sc, vnum, max_voxels, compact, batch, n_ch, plane, canvas);
         else
             k_canvas_fill<MODE, false, 16, 4, 2304><<<blocks6, 128, 0, stream>>>(map, feats, sv, sc, vnum, max_voxels, compact, batch, n_ch, plane, canvas);
+        return cudaGetLastError();
+    }
+    if ((variant == 7 || variant == 8) && (plane % 8 != 0 || !al32)) variant = 0;
+    if (variant == 7 || variant == 8) {   // experiments on the 256-cell warp: 7 = 4 warps per CTA, 8 = registers capped for 5 CTAs per SM
+        const long long w78 = (long long)((plane + 255) / 256) * batch;
+        if (variant == 7) {
+            const unsigned b7 = (unsigned)((w78 + 3) / 4);
+            if (feat4) k_canvas_fill<MODE, true, 8, 4, 1152><<<b7, 128, 0, stream>>>(map, feats, sv, sc, vnum, max_voxels, compact, batch, n_ch, plane, canvas);
+            else k_canvas_fill<MODE, false, 8, 4, 1152><<<b7, 128, 0, stream>>>(map, feats, sv, sc, vnum, max_voxels, compact, batch, n_ch, plane, canvas);
+        } else {
+            const unsigned b8 = (unsigned)((w78 + 7) / 8);
+            if (feat4) k_canvas_fill<MODE, true, 8, 8, 1024, 5><<<b8, 256, 0, stream>>>(map, feats, sv, sc, vnum, max_voxels, compact, batch, n_ch, plane, canvas);
+            else k_canvas_fill<MODE, false, 8, 8, 1024, 5><<<b8, 256, 0, stream>>>(map, feats, sv, sc, vnum, max_voxels, compact, batch, n_ch, plane, canvas);
+        }
         return cudaGetLastError();
     }
     const bool wide = variant == 1 && (plane % 8 == 0) && al32;   // else variant 0

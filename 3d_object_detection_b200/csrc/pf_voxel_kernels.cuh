@@ -307,11 +307,11 @@ __global__ void __launch_bounds__(kTileWarps * 32) k_tile_rank(Params p, Work w,
 // ---------------------------------------------------------------------------------------------------------
 // K5: saturating exclusive scan down every voxel column of the count matrix (in place), totals -> vcount.
 // A thread owns 4 adjacent columns (one 32-bit word per row) and walks all rows with 16 independent loads in flight;
-// per-byte saturating adds (__vaddus4) cap every counter at kCountCap = 255.  (Round 2 also tried splitting the rows of
+// every counter saturates at kCountCap = 255.  (Round 2 also tried splitting the rows of
 // a column over the warps of a CTA so that every thread issues all its loads at once: same 10 us at 20 cm x 8, 61 instead
 // of 38 us at 10 cm x 32 -- profiles/r2_chain_experiments.md E3.)
 __global__ void __launch_bounds__(128) k_column_scan(Params p, Work w, const int32_t *__restrict__ frame_offsets,
-                                                            int max_frame_points)
+                                                     int max_frame_points)
 {
     const int f = blockIdx.y;
     int n = frame_offsets[f + 1] - frame_offsets[f];
@@ -322,7 +322,7 @@ __global__ void __launch_bounds__(128) k_column_scan(Params p, Work w, const int
     if (col >= n_vox) return;
     uint32_t *m = reinterpret_cast<uint32_t *>(w.cnt + (size_t)f * p.tiles_cap * p.vcols + col);
     const size_t row_words = p.vcols / 4;
-    uint32_t run = 0;
+    int run[4] = {0, 0, 0, 0};
     constexpr int U = 16;
     for (int t0 = 0; t0 < n_tiles; t0 += U) {
         uint32_t v[U];
@@ -331,16 +331,20 @@ __global__ void __launch_bounds__(128) k_column_scan(Params p, Work w, const int
 #pragma unroll
         for (int u = 0; u < U; ++u) {
             if (t0 + u < n_tiles) {
-                m[(size_t)(t0 + u) * row_words] = run;
-                run = __vaddus4(run, v[u]);
+                uint32_t out = 0;
+#pragma unroll
+                for (int k = 0; k < 4; ++k) {
+                    out |= (uint32_t)run[k] << (8 * k);
+                    const int s = run[k] + (int)((v[u] >> (8 * k)) & 0xffu);
+                    run[k] = s < kCountCap ? s : kCountCap;
+                }
+                m[(size_t)(t0 + u) * row_words] = out;
             }
         }
     }
 #pragma unroll
-    for (int k = 0; k < 4; ++k) {
-        const int c = (int)((run >> (8 * k)) & 0xffu);
-        if (col + k < n_vox) w.vcount[(size_t)f * p.max_voxels + col + k] = c < p.P ? c : p.P;
-    }
+    for (int k = 0; k < 4; ++k)
+        if (col + k < n_vox) w.vcount[(size_t)f * p.max_voxels + col + k] = run[k] < p.P ? run[k] : p.P;
 }
 
 // ---------------------------------------------------------------------------------------------------------

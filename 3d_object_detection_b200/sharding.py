@@ -127,50 +127,60 @@ class _GpuWorker:
         """Move `frames` (at most B arrays of shape (N, F), float32) onto the GPU and enqueue the next slot's graph;
         returns a token for :meth:`finish`.  Does not wait for the GPU.  A frame may be
           * a numpy array (pageable host memory, what a dataset hands over): copied into the slot's pinned staging
-            buffer by pf_stage_copy, then one asynchronous H2D;
+            buffer, then one asynchronous H2D;
           * a pinned torch CPU tensor: one asynchronous H2D straight from it, no staging copy (the caller must not
             rewrite it before the batch has finished);
-          * a CUDA tensor on this GPU: a device-to-device copy."""
+          * a CUDA tensor on this GPU: a device-to-device copy.
+        All of it is ONE library call (pf_upload_frames), so the worker thread gives the interpreter lock up for the whole
+        copy phase."""
+        import ctypes as C
         torch = self.torch
         s = self.slots[self.turn % len(self.slots)]
         self.turn += 1
         n = len(frames)
         if n > self.B:
             raise ValueError(f"{n} frames for a worker built for {self.B}")
-        lib = self._lib.load()
-        offs = s["np_offs"]
-        pos = 0
-        with torch.cuda.device(self.dev), torch.cuda.stream(s["stream"]):
-            s["e0"].record(s["stream"])
-            for b in range(self.B):
-                offs[b] = pos
-                if b >= n:
-                    continue
-                f = frames[b]
-                is_t = torch.is_tensor(f)
-                if (f.dtype != torch.float32) if is_t else (str(getattr(f, "dtype", None)) != "float32"):
-                    raise TypeError(f"frames must be float32, got {getattr(f, 'dtype', type(f).__name__)}")
-                m = int(f.shape[0])
-                if f.ndim != 2 or m > self.cap or int(f.shape[1]) != self.F:
-                    raise ValueError(f"frame of shape {tuple(f.shape)} for capacity ({self.cap}, {self.F})")
-                if m:
-                    dst = s["d_pts"][pos:pos + m]
-                    if is_t:
-                        dst.copy_(f.contiguous(), non_blocking=True)
-                    else:
-                        src = f if f.flags.c_contiguous else f.copy()
-                        self._lib.check(lib.pf_stage_copy(s["np_pts"][pos:].ctypes.data, src.ctypes.data, src.nbytes,
-                                                          self.threads), "pf_stage_copy")
-                        dst.copy_(s["h_pts"][pos:pos + m], non_blocking=True)
-                pos += m
-            offs[self.B] = pos
-            s["graph"].replay()
-            s["e1"].record(s["stream"])
+        ptrs, rows, kinds, keep = (C.c_void_p * self.B)(), (C.c_int64 * self.B)(), (C.c_int32 * self.B)(), []
+        total = 0
+        for b, f in enumerate(frames):
+            is_t = torch.is_tensor(f)
+            if (f.dtype != torch.float32) if is_t else (str(getattr(f, "dtype", None)) != "float32"):
+                raise TypeError(f"frames must be float32, got {getattr(f, 'dtype', type(f).__name__)}")
+            m = int(f.shape[0])
+            if f.ndim != 2 or int(f.shape[1]) != self.F:
+                raise ValueError(f"frame of shape {tuple(f.shape)} for {self.F} floats per point")
+            total += m
+            if is_t:
+                f = f.contiguous()
+                if f.is_cuda and f.device.index != self.device:
+                    f = f.to(self.dev)
+                ptrs[b], kinds[b] = f.data_ptr(), 2 if f.is_cuda else (1 if f.is_pinned() else 0)
+            else:
+                if not f.flags.c_contiguous:
+                    f = f.copy()
+                ptrs[b], kinds[b] = f.ctypes.data, 0
+            keep.append(f)                                   # the (possibly re-laid-out) sources must outlive the copies
+            rows[b] = m
+        if total > self.B * self.cap:
+            raise ValueError(f"{total} points for a worker built for {self.B} x {self.cap}")
+        if any(int(r) > self.cap for r in rows):
+            raise ValueError(f"a frame exceeds the capacity of {self.cap} points")
+        torch.cuda.set_device(self.dev)                      # thread-local: this worker thread only
+        torch.cuda.set_stream(s["stream"])
+        st = s["stream"]
+        s["e0"].record(st)
+        self._lib.check(self._lib.load().pf_upload_frames(
+            s["d_pts"].data_ptr(), s["h_pts"].data_ptr(), ptrs, rows, kinds, n, self.B, 4 * self.F, self.threads,
+            s["h_offs"].data_ptr(), st.cuda_stream), "pf_upload_frames")
+        s["graph"].replay()
+        s["e1"].record(st)
+        s["keep"] = keep
         return s, list(frame_ids), n
 
     def finish(self, token):
         s, frame_ids, n = token
         s["e1"].synchronize()
+        s["keep"] = None
         fe = s["fe"]
         return ShardResult(self.device, frame_ids, fe.canvas[:n], fe.coors[:n * fe.max_voxels], fe.voxel_num[:n],
                            s["np_cnt"][:n].copy(), s["e0"].elapsed_time(s["e1"]))
@@ -199,7 +209,7 @@ class ShardedFrontEnd:
     filled from each worker's `pillar` stand-in tensor (what bench.py's headline does: the PFN is not on the path)."""
 
     def __init__(self, config, devices=None, frames_per_device=8, max_points_per_frame=None, n_channels=64, pfn=None,
-                 depth=3, placement="spread", stage_threads=2, _worker_factory=None):
+                 depth=3, placement="spread", stage_threads=None, _worker_factory=None):
         import queue
         import threading
         if _worker_factory is None:
@@ -212,6 +222,10 @@ class ShardedFrontEnd:
                 devices = n_vis
             if isinstance(devices, int):
                 devices = place_devices(devices, n_vis, placement)
+            if stage_threads is None:      # host threads per worker for the pageable -> pinned copy: the workers already run
+                import os                 # side by side, so from 4 GPUs on each copies with its own thread only
+                cores = len(os.sched_getaffinity(0)) if hasattr(os, "sched_getaffinity") else (os.cpu_count() or 1)
+                stage_threads = 1 if len(devices) >= 4 else max(1, min(4, cores // (2 * len(devices))))
             cap = int(max_points_per_frame or config.get("frame_points", 0) or 0)
             if cap < 1:
                 raise ValueError("max_points_per_frame is required")

@@ -96,6 +96,18 @@ PF_API int pf_stage_copy(void *dst, const void *src, size_t bytes, int threads);
 PF_API int pf_copy3(void *dst0, const void *src0, size_t bytes0, void *dst1, const void *src1, size_t bytes1,
                     void *dst2, const void *src2, size_t bytes2, void *stream);
 
+/* Batched multi-frame upload (the collate + H2D of row N3, framework/utils.py:23-48, for a list of per-frame arrays): copies
+ * `n_frames` frames back to back into `device_points` on `stream` and writes the frame offsets (n_slots + 1 int32, frames
+ * beyond n_frames empty) into `pinned_offsets`, host memory the caller then copies / captures to the device.
+ *   kinds[b] = 0: frames[b] is pageable host memory -- copied into `pinned_stage` (same layout as device_points) by up to
+ *                 `threads` host threads, then one asynchronous H2D;
+ *   kinds[b] = 1: pinned host memory -- one asynchronous H2D straight from it;   kinds[b] = 2: device memory (D2D).
+ * rows[b] = points in frame b; row_bytes = bytes per point row.  One call per batch, so a Python worker thread holds the
+ * interpreter lock for microseconds, not for the copies. */
+PF_API int pf_upload_frames(void *device_points, void *pinned_stage, const void *const *frames, const int64_t *rows,
+                            const int32_t *kinds, int n_frames, int n_slots, int row_bytes, int threads,
+                            int32_t *pinned_offsets, void *stream);
+
 /* Diagnostics: with timing enabled every voxelise / fill call of this handle records a CUDA event after each of
  * its kernels (eager launches only -- do not capture such a call into a graph).  pf_debug_stage_times waits for
  * the last call and writes the 8 stage durations in milliseconds (quantize, assign, tile_rank, column_scan, slot,

@@ -18,6 +18,13 @@ for g in 20cm nuscene 10cm; do
   timeout 120 python tools/stage_times.py --grid $g > $o/${tag}_stage_$g.txt 2>&1
   timeout 120 python tools/stage_times.py --grid $g --pfn > $o/${tag}_stage_${g}_pfn.txt 2>&1
 done
+B="--no-cpu-baseline --no-postprocess --no-anchor-mask --no-single --no-pfn --steps 100 --device-pipelines 1"
+for v in 1 7 8; do
+  PF_FILL_VARIANT=$v timeout 300 python bench.py --grid 20cm $B > $o/${tag}_fillx${v}_20cm.json 2> /dev/null
+  PF_FILL_VARIANT=$v timeout 300 python bench.py --grid nuscene $B > $o/${tag}_fillx${v}_nuscene.json 2> /dev/null
+done
+timeout 300 python bench.py --sharded --gpus 1 --steps 100 > $o/${tag}_sharded_n1.json 2> $o/${tag}_sharded_n1.err
+timeout 300 python bench.py --sharded --pinned-frames --gpus 1 --steps 100 > $o/${tag}_sharded_pinned_n1.json 2> $o/${tag}_sharded_pinned_n1.err
 timeout 120 python tools/frame_probe.py > $o/${tag}_frame_probe.txt 2>&1
 timeout 120 python tools/frame_probe.py --grid nuscene >> $o/${tag}_frame_probe.txt 2>&1
 L="--steps 30 --warmup 5 --no-cpu-baseline --no-pfn --no-single --no-anchor-mask --no-postprocess"
@@ -27,11 +34,11 @@ timeout 900 ncu --metrics gpu__time_duration.sum --clock-control none -c 600 --c
 cat $o/${tag}_pytest.log
 python - <<'PY'
 import json, glob
-for f in sorted(glob.glob("gpurun_out/r2fin_bench*.json")):
+for f in sorted(glob.glob("gpurun_out/r2fin_*.json")):
     try:
-        d = json.load(open(f))
+        d = json.loads([l for l in open(f).read().splitlines() if l.startswith("{")][-1])
         print(f.split("/")[-1], "ms/step", round(d["ms_per_step"], 4), "G", round(d["value"] / 1e9, 3), "serial", round(d.get("serial", {}).get("ms_per_step", 0), 4),
-              "e2e ms", round(d["e2e"].get("ms_per_step", 0), 4), "fill frac", round(d.get("roofline", {}).get("frac", 0), 3), "step frac", round(d.get("e2e_hbm_frac", 0), 3))
+              "e2e ms", round(d["e2e"].get("ms_per_step", 0), 4), "fill us", round(1e3 * d.get("stages_ms", {}).get("scatter", 0), 1), "fill frac", round(d.get("roofline", {}).get("frac", 0), 3), "step frac", round(d.get("e2e_hbm_frac", 0), 3))
     except Exception as e:
         print(f, "ERR", e)
 PY
