@@ -307,7 +307,7 @@ __global__ void __launch_bounds__(kTileWarps * 32) k_tile_rank(Params p, Work w,
 // ---------------------------------------------------------------------------------------------------------
 // K5: saturating exclusive scan down every voxel column of the count matrix (in place), totals -> vcount.
 // A thread owns 4 adjacent columns (one 32-bit word per row) and walks all rows with 16 independent loads in flight;
-// every counter saturates at kCountCap = 255.  (Round 2 also tried splitting the rows of
+// every counter saturates at kCountCap = 255.  (__vaddus4 is emulated on sm_100: 72 instead of 39 us at 10 cm x 32.  Round 2 also tried splitting the rows of
 // a column over the warps of a CTA so that every thread issues all its loads at once: same 10 us at 20 cm x 8, 61 instead
 // of 38 us at 10 cm x 32 -- profiles/r2_chain_experiments.md E3.)
 __global__ void __launch_bounds__(128) k_column_scan(Params p, Work w, const int32_t *__restrict__ frame_offsets,

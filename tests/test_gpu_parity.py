@@ -255,3 +255,64 @@ def test_pointnet_module(pfm):
     assert out.shape == (len(n), 64)
     assert torch.allclose(out, want, rtol=1e-4, atol=1e-4)
     vg.close()
+
+
+# ------------------------------------------------------------------------------------------------ single-frame fast path
+def test_generate_outputs_are_owned_by_the_caller(pfm):
+    """The numpy arrays generate() returns are views of pinned blocks from a recycling pool: results a caller keeps must
+    stay intact over any number of later calls (more of them than the pool holds), a block is reused only after every
+    array from it has been released, and device outputs are fresh tensors."""
+    import gc
+    cfg = cfgmod.builtin_config("20cm")
+    cfg["max_voxels"] = 1200
+    geom = cfgmod.derive_grid(cfg)
+    vg = pfm.VoxelGenerator(dict(cfg))
+    frames = [np.ascontiguousarray(synth.make_frame(["S1", "S3", "S2"][i % 3], geom, 3000 + 517 * i, 800 + i, 400), np.float32)
+              for i in range(12)]
+    want = [oracle.generate(geom, f, 1200, 15) for f in frames]
+    kept = [vg.generate(f) for f in frames]                    # 12 live results > the 8 pooled blocks -> pageable fall-back
+    for i, (g, w) in enumerate(zip(kept, want)):
+        util.assert_vox_equal(g, w, f"kept result {i}")
+    assert len(vg._pool) == 8 and not any(b.free() for b in vg._pool)
+    first_block = vg._pool[0]
+    del kept, g
+    gc.collect()
+    assert all(b.free() for b in vg._pool)
+    again = vg.generate(frames[3])
+    assert again[0].base is first_block.nv                     # a released block is handed out again
+    util.assert_vox_equal(again, want[3], "recycled block")
+    dev = [vg.generate(f, device_outputs=True) for f in frames[:3]]
+    for i, d in enumerate(dev):                                # device outputs: fresh tensors, untouched by later calls
+        util.assert_vox_equal(tuple(_np(t) for t in d), want[i], f"device result {i}")
+    assert len({d[0].data_ptr() for d in dev}) == 3
+    # a longer frame (another capacity bucket) and another feature count on the same instance
+    big = np.ascontiguousarray(synth.make_frame("S3", geom, 40000, 5), np.float32)
+    util.assert_vox_equal(vg.generate(big), oracle.generate(geom, big, 1200, 15), "second capacity bucket")
+    five = np.ascontiguousarray(np.concatenate([frames[0], frames[0][:, :1]], axis=1))
+    util.assert_vox_equal(vg.generate(five), oracle.generate(geom, five, 1200, 15), "F = 5 on the same instance")
+    util.assert_vox_equal(vg.generate(frames[1]), want[1], "back to F = 4")
+    vg.close()
+
+
+def test_generate_and_scatter_matches_the_module_sequence(pfm):
+    """generate_and_scatter (one graph: H2D, voxelise, decorate + fused PFN, fill) against generate -> PointNet.eval() ->
+    PointPillarsScatter on the same frames, frame after frame on one instance (sizes change between calls)."""
+    cfg = cfgmod.builtin_config("nuscene")
+    cfg["max_voxels"] = 2000
+    geom = cfgmod.derive_grid(cfg)
+    torch.manual_seed(3)
+    net = pfm.PointNet(4, cfg["voxel_size"], geom.offset).cuda().eval()
+    sc = pfm.PointPillarsScatter(1, geom.grid_size, 64)
+    vg = pfm.VoxelGenerator(dict(cfg))
+    for i, (kind, n) in enumerate([("S1", 9000), ("S3", 6000), ("S1", 0), ("S2", 12800), ("S1", 9000)]):
+        pts = np.ascontiguousarray(synth.make_frame(kind, geom, max(n, 8), 900 + i, 700)[:n], np.float32)
+        with torch.no_grad():
+            canvas, coors, v = vg.generate_and_scatter(pts, net)
+            got = canvas.clone()
+            wv, wc, wn = oracle.generate(geom, pts, 2000, 100)
+            assert v == len(wn) and np.array_equal(_np(coors)[:, :3], wc)
+            dv, dc, dn = vg.generate(pts, device_outputs=True)
+            want = sc(net(dv, dn, dc).reshape(-1, 64), dc) if v else torch.zeros_like(got)
+        assert torch.equal(got != 0, want != 0) or torch.equal(got == 0, want == 0), f"frame {i}: occupancy pattern"
+        assert torch.allclose(got, want, rtol=1e-5, atol=1e-5), f"frame {i} ({kind}, {n} points): {(got - want).abs().max()}"
+    vg.close()
