@@ -12,7 +12,8 @@ LIB_PATH = Path(__file__).resolve().parent / "lib" / "libpillarfront.so"
 EXPORTS = ["pf_version", "pf_last_error_string", "pf_create", "pf_destroy", "pf_workspace_bytes",
            "pf_voxelize", "pf_voxelize_decorate", "pf_voxelize_pfn", "pf_pfn", "pf_decorate", "pf_scatter", "pf_scatter_from_map",
            "pf_scatter_backward", "pf_anchor_mask", "pf_nms", "pf_nms_scratch_bytes",
-           "pf_debug_stage_timing", "pf_debug_stage_times", "pf_debug_set_fill_variant", "pf_discard_cell_map", "pf_stage_copy", "pf_copy3", "pf_upload_frames",
+           "pf_debug_stage_timing", "pf_debug_stage_times", "pf_debug_set_fill_variant", "pf_discard_cell_map", "pf_stage_copy", "pf_copy3", "pf_upload_frames", "pf_runner_create", "pf_runner_set_slot", "pf_runner_submit",
+           "pf_runner_wait", "pf_runner_destroy", "pf_runner_last_error",
            "pf_postprocess", "pf_post_scratch_bytes", "pf_post_scratch_layout"]
 
 
@@ -101,6 +102,18 @@ def load():
     L.pf_upload_frames.restype = C.c_int
     L.pf_upload_frames.argtypes = [_p, _p, C.POINTER(_p), C.POINTER(C.c_int64), C.POINTER(C.c_int32), C.c_int, C.c_int, C.c_int,
                                    C.c_int, _p, _p]
+    L.pf_runner_create.restype = C.c_int
+    L.pf_runner_create.argtypes = [C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, C.POINTER(_p)]
+    L.pf_runner_set_slot.restype = C.c_int
+    L.pf_runner_set_slot.argtypes = [_p, C.c_int, _p, _p, _p, _p, _p]
+    L.pf_runner_submit.restype = C.c_longlong
+    L.pf_runner_submit.argtypes = [_p, C.POINTER(_p), C.POINTER(C.c_int64), C.POINTER(C.c_int32), C.c_int]
+    L.pf_runner_wait.restype = C.c_int
+    L.pf_runner_wait.argtypes = [_p, C.c_longlong, C.POINTER(C.c_float)]
+    L.pf_runner_destroy.restype = C.c_int
+    L.pf_runner_destroy.argtypes = [_p]
+    L.pf_runner_last_error.restype = C.c_char_p
+    L.pf_runner_last_error.argtypes = []
     L.pf_copy3.restype = C.c_int
     L.pf_copy3.argtypes = [_p, _p, C.c_size_t, _p, _p, C.c_size_t, _p, _p, C.c_size_t, _p]
     L.pf_debug_set_fill_variant.restype = C.c_int

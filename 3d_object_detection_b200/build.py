@@ -17,7 +17,7 @@ ROOT = PKG.parent
 CSRC = PKG / "csrc"
 LIB_DIR = PKG / "lib"
 LIB = LIB_DIR / "libpillarfront.so"
-SOURCES = ["pf_api.cu", "pf_voxelize.cu", "pf_gather.cu", "pf_scatter.cu", "pf_anchor.cu", "pf_nms.cu", "pf_post.cu"]
+SOURCES = ["pf_api.cu", "pf_voxelize.cu", "pf_gather.cu", "pf_scatter.cu", "pf_anchor.cu", "pf_nms.cu", "pf_post.cu", "pf_runner.cu"]
 NVCC_FLAGS = ["-gencode", "arch=compute_100a,code=sm_100a", "-O3", "-lineinfo", "-std=c++17",
               "--shared", "-Xcompiler", "-fPIC,-Wall,-Wextra,-fvisibility=hidden,-fopenmp", "-lgomp",
               "-Xptxas", "-v", "--fmad=false"]

@@ -260,7 +260,13 @@ int pf_upload_frames(void *device_points, void *pinned_stage, const void *const 
         const size_t bytes = (size_t)rows[b] * row_bytes;
         char *dst = static_cast<char *>(device_points) + (size_t)pos * row_bytes;
         const void *src = frames[b];
-        if (kinds[b] == 0) {                    // pageable host memory: through the pinned staging buffer
+        int kind = kinds[b];
+        if (kind < 0) {                         // ask the driver what kind of memory this is
+            cudaPointerAttributes at{};
+            if (cudaPointerGetAttributes(&at, src) != cudaSuccess) cudaGetLastError();
+            kind = at.type == cudaMemoryTypeDevice || at.type == cudaMemoryTypeManaged ? 2 : (at.type == cudaMemoryTypeHost ? 1 : 0);
+        }
+        if (kind == 0) {                        // pageable host memory: through the pinned staging buffer
             if (!pinned_stage) return fail(PF_ERR_INVALID_ARGUMENT, "pf_upload_frames: pageable frame without a staging buffer");
             char *stage = static_cast<char *>(pinned_stage) + (size_t)pos * row_bytes;
             pf_stage_copy(stage, src, bytes, threads);

@@ -1,5 +1,7 @@
 // Host-side launchers of the voxelisation chain (kernels: pf_voxel_kernels.cuh, pf_gather.cu) and the generic-F
 // gather / decoration kernel.  Reference: framework/voxel_generator.py:28-40, 82-106.
+#include <cstdlib>
+
 #include "pf_voxel_kernels.cuh"
 
 namespace pf {
@@ -225,7 +227,8 @@ cudaError_t launch_voxelize(const Params &p, const Work &w, const VoxelizeArgs &
     constexpr int kPtsPerCta = 256 * kQPer;
     const dim3 g_pts((npts + kPtsPerCta - 1) / kPtsPerCta, B), g_tiles(tiles, B);
     // leading 1/16 of every frame first (see k_quantize); small frames go in one launch
-    const int split = npts >= 32 * kPtsPerCta ? ((npts / 16 + kPtsPerCta - 1) / kPtsPerCta) * kPtsPerCta : npts;
+    static const int split_den = [] { const char *e = getenv("PF_QUANTIZE_SPLIT"); const int d = e ? atoi(e) : 16; return d < 0 ? 16 : d; }();   // experiments: 0 = one launch
+    const int split = (split_den > 1 && npts >= 32 * kPtsPerCta) ? ((npts / split_den + kPtsPerCta - 1) / kPtsPerCta) * kPtsPerCta : npts;
     mark(w, kEvStart, stream);
     for (int pass = 0; pass < 2; ++pass) {
         const int lo = pass == 0 ? 0 : split, hi = pass == 0 ? split : npts;

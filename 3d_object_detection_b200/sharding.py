@@ -62,18 +62,35 @@ class ShardResult:
     """What one GPU produced for its share of a submitted batch.  `canvas` (n, C, nx, ny), `coors` (n * max_voxels, 4)
     and `voxel_num` (n,) are CUDA tensors on `device`, views of the worker's buffers: valid until that worker has been
     handed `depth - 1` further batches (the worker stages batch k+1 while batch k runs, so depth >= 2; the default is 3).
-    `counts` is `voxel_num` on the host."""
+    `counts` is `voxel_num` on the host; `device_ms` the CUDA-event time of the batch (upload + graph; -1 if the slot had
+    already been reused when the batch was waited for)."""
 
-    __slots__ = ("device", "frame_ids", "canvas", "coors", "voxel_num", "counts", "device_ms")
+    __slots__ = ("device", "frame_ids", "counts", "_fe", "_n", "_ev")
 
-    def __init__(self, device, frame_ids, canvas, coors, voxel_num, counts, device_ms):
-        self.device, self.frame_ids, self.canvas, self.coors = device, frame_ids, canvas, coors
-        self.voxel_num, self.counts, self.device_ms = voxel_num, counts, device_ms
+    def __init__(self, device, frame_ids, fe, n, counts, ev):
+        self.device, self.frame_ids, self.counts = device, frame_ids, counts
+        self._fe, self._n, self._ev = fe, n, ev
+
+    @property
+    def canvas(self):
+        return self._fe.canvas[:self._n]
+
+    @property
+    def coors(self):
+        return self._fe.coors[:self._n * self._fe.max_voxels]
+
+    @property
+    def voxel_num(self):
+        return self._fe.voxel_num[:self._n]
+
+    @property
+    def device_ms(self):
+        return self._ev
 
 
 class _GpuWorker:
     """One GPU: `depth` PillarFrontEnd replicas (workspace, outputs, pinned staging, one stream and one CUDA graph
-    each), used in turn; the graph holds H2D of the staged frames + offsets, voxelise + decorate (+ fused PFN), canvas
+    each), used in turn by the GPU's native runner (pf_runner_*); the graph holds H2D of the staged frames + offsets, voxelise + decorate (+ fused PFN), canvas
     fill, D2H of the voxel counts; the points themselves are copied in front of it, one copy per frame."""
 
     def __init__(self, config, device, frames_per_device, max_points_per_frame, n_channels, pfn, depth, stage_threads):
@@ -112,7 +129,15 @@ class _GpuWorker:
                     with torch.cuda.graph(s["graph"], stream=s["stream"]):
                         self._body(s)
                 self.slots.append(s)
-        self.turn = 0
+        import ctypes as C
+        # the native runner: one host thread of the library per GPU uploads, launches and is waited on -- no interpreter
+        # lock on the data path.  Slot k of the runner = self.slots[k]: its instantiated graph, stream and buffers.
+        L = _lib.load()
+        self._runner = C.c_void_p()
+        _lib.check(L.pf_runner_create(self.device, depth, self.B, 4 * self.F, self.threads, C.byref(self._runner)), "pf_runner_create")
+        for k, s in enumerate(self.slots):
+            _lib.check(L.pf_runner_set_slot(self._runner, k, s["graph"].raw_cuda_graph_exec(), s["stream"].cuda_stream,
+                                            s["d_pts"].data_ptr(), s["h_pts"].data_ptr(), s["h_offs"].data_ptr()), "pf_runner_set_slot")
 
     def _body(self, s):
         # the points are copied in front of the graph, frame by frame, from wherever they live (launch())
@@ -131,82 +156,110 @@ class _GpuWorker:
           * a pinned torch CPU tensor: one asynchronous H2D straight from it, no staging copy (the caller must not
             rewrite it before the batch has finished);
           * a CUDA tensor on this GPU: a device-to-device copy.
-        All of it is ONE library call (pf_upload_frames), so the worker thread gives the interpreter lock up for the whole
-        copy phase."""
+          (it must be complete: the copy runs on the runner's stream, not on the one that produced the tensor).
+        Only pointers are handed to the GPU's native runner (pf_runner_submit); its thread does the copies and the launch."""
         import ctypes as C
         torch = self.torch
-        s = self.slots[self.turn % len(self.slots)]
-        self.turn += 1
         n = len(frames)
         if n > self.B:
             raise ValueError(f"{n} frames for a worker built for {self.B}")
         ptrs, rows, kinds, keep = (C.c_void_p * self.B)(), (C.c_int64 * self.B)(), (C.c_int32 * self.B)(), []
         total = 0
+        f32 = torch.float32
         for b, f in enumerate(frames):
-            is_t = torch.is_tensor(f)
-            if (f.dtype != torch.float32) if is_t else (str(getattr(f, "dtype", None)) != "float32"):
-                raise TypeError(f"frames must be float32, got {getattr(f, 'dtype', type(f).__name__)}")
-            m = int(f.shape[0])
-            if f.ndim != 2 or int(f.shape[1]) != self.F:
-                raise ValueError(f"frame of shape {tuple(f.shape)} for {self.F} floats per point")
-            total += m
-            if is_t:
-                f = f.contiguous()
+            if isinstance(f, torch.Tensor):
+                if f.dtype != f32:
+                    raise TypeError(f"frames must be float32, got {f.dtype}")
+                if not f.is_contiguous():
+                    f = f.contiguous()
                 if f.is_cuda and f.device.index != self.device:
                     f = f.to(self.dev)
-                ptrs[b], kinds[b] = f.data_ptr(), 2 if f.is_cuda else (1 if f.is_pinned() else 0)
+                ptrs[b], kinds[b] = f.data_ptr(), 2 if f.is_cuda else -1      # host tensor: pinned or not, the library asks the driver
             else:
+                if str(getattr(f, "dtype", None)) != "float32":
+                    raise TypeError(f"frames must be float32, got {getattr(f, 'dtype', type(f).__name__)}")
                 if not f.flags.c_contiguous:
                     f = f.copy()
                 ptrs[b], kinds[b] = f.ctypes.data, 0
+            shp = f.shape
+            if len(shp) != 2 or int(shp[1]) != self.F:
+                raise ValueError(f"frame of shape {tuple(shp)} for {self.F} floats per point")
             keep.append(f)                                   # the (possibly re-laid-out) sources must outlive the copies
-            rows[b] = m
+            rows[b] = int(shp[0])
+            total += int(shp[0])
         if total > self.B * self.cap:
             raise ValueError(f"{total} points for a worker built for {self.B} x {self.cap}")
         if any(int(r) > self.cap for r in rows):
             raise ValueError(f"a frame exceeds the capacity of {self.cap} points")
-        torch.cuda.set_device(self.dev)                      # thread-local: this worker thread only
-        torch.cuda.set_stream(s["stream"])
-        st = s["stream"]
-        s["e0"].record(st)
-        self._lib.check(self._lib.load().pf_upload_frames(
-            s["d_pts"].data_ptr(), s["h_pts"].data_ptr(), ptrs, rows, kinds, n, self.B, 4 * self.F, self.threads,
-            s["h_offs"].data_ptr(), st.cuda_stream), "pf_upload_frames")
-        s["graph"].replay()
-        s["e1"].record(st)
-        s["keep"] = keep
-        return s, list(frame_ids), n
+        L = self._lib.load()
+        ticket = L.pf_runner_submit(self._runner, ptrs, rows, kinds, n)
+        if ticket < 0:
+            raise self._lib.PillarFrontError(f"pf_runner_submit failed (status {ticket}): {L.pf_runner_last_error().decode()}")
+        return ticket, keep, list(frame_ids), n
 
     def finish(self, token):
-        s, frame_ids, n = token
-        s["e1"].synchronize()
-        s["keep"] = None
-        fe = s["fe"]
-        return ShardResult(self.device, frame_ids, fe.canvas[:n], fe.coors[:n * fe.max_voxels], fe.voxel_num[:n],
-                           s["np_cnt"][:n].copy(), s["e0"].elapsed_time(s["e1"]))
+        import ctypes as C
+        ticket, _keep, frame_ids, n = token
+        L = self._lib.load()
+        ms = C.c_float(0.0)
+        rc = L.pf_runner_wait(self._runner, ticket, C.byref(ms))      # blocks in the library: the interpreter lock is free
+        if rc != 0:
+            raise self._lib.PillarFrontError(f"batch {ticket} on GPU {self.device} failed (status {rc}): {L.pf_runner_last_error().decode()}")
+        s = self.slots[ticket % len(self.slots)]
+        return ShardResult(self.device, frame_ids, s["fe"], n, s["np_cnt"][:n].copy(), float(ms.value))
 
     def run(self, frame_ids, frames):
         return self.finish(self.launch(frame_ids, frames))
 
     def close(self):
+        if getattr(self, "_runner", None):
+            self._lib.load().pf_runner_destroy(self._runner)      # drains the queue, joins the thread
+            self._runner = None
         for s in self.slots:
             s["graph"] = None
             s["fe"].close()
         self.slots = []
 
 
+class _NativeFuture:
+    """Future-like handle of one batch on one GPU's native runner: result() waits inside the library."""
+
+    __slots__ = ("_worker", "_token", "_result", "_exc")
+
+    def __init__(self, worker, token):
+        self._worker, self._token, self._result, self._exc = worker, token, None, None
+
+    def result(self, timeout=None):
+        if self._token is not None:
+            try:
+                self._result = self._worker.finish(self._token)
+            except BaseException as exc:
+                self._exc = exc
+            self._token = None               # releases the frames kept alive for the upload
+        if self._exc is not None:
+            raise self._exc
+        return self._result
+
+    def done(self):
+        return self._token is None
+
+
 class ShardedFrontEnd:
-    """Frame-sharded front end over the GPUs of one box: ``submit(frames)`` deals frame ``b`` to GPU ``b mod G`` (one
-    worker thread per GPU -- the ctypes calls and CUDA waits release the GIL), every GPU runs its own replica of the
-    whole path on its share (pinned staging, one CUDA graph per step), and nothing crosses between GPUs: no NCCL, the
-    canvases stay where that GPU's backbone replica would read them.
+    """Frame-sharded front end over the GPUs of one box: ``submit(frames)`` deals frame ``b`` to GPU ``b mod G``, every GPU
+    runs its own replica of the whole path on its share (pinned staging, one CUDA graph per step), and nothing crosses
+    between GPUs: no NCCL, the canvases stay where that GPU's backbone replica would read them.  Each GPU is
+    driven by ONE NATIVE THREAD of the library (``pf_runner_*``, csrc/pf_runner.cu): ``submit`` hands it pointers and
+    returns, the thread uploads the frames and launches the graph, ``result()`` waits inside the library -- the interpreter
+    lock is not on the data path.
 
         sfe = ShardedFrontEnd(config, devices=8, frames_per_device=8, pfn=point_net)
-        futures = sfe.submit(list_of_64_numpy_frames)        # one Future per GPU -> ShardResult
-        results = sfe.run(list_of_64_numpy_frames)           # the same, waited for, in GPU order
+        futures = sfe.submit(list_of_64_frames)              # one future per GPU -> ShardResult
+        results = sfe.run(list_of_64_frames)                 # the same, waited for, in GPU order
 
     `pfn`: a PointNet (eval mode) replicated onto every GPU and fused into the voxeliser; without it the canvas is
-    filled from each worker's `pillar` stand-in tensor (what bench.py's headline does: the PFN is not on the path)."""
+    filled from each worker's `pillar` stand-in tensor (what bench.py's headline does: the PFN is not on the path).
+    A result's tensors are views of one of the worker's `depth` buffer sets: valid until `depth` further batches have been
+    submitted to that GPU."""
 
     def __init__(self, config, devices=None, frames_per_device=8, max_points_per_frame=None, n_channels=64, pfn=None,
                  depth=3, placement="spread", stage_threads=None, _worker_factory=None):
@@ -222,7 +275,7 @@ class ShardedFrontEnd:
                 devices = n_vis
             if isinstance(devices, int):
                 devices = place_devices(devices, n_vis, placement)
-            if stage_threads is None:      # host threads per worker for the pageable -> pinned copy: the workers already run
+            if stage_threads is None:      # host threads per GPU for the pageable -> pinned copy: the runners already work
                 import os                 # side by side, so from 4 GPUs on each copies with its own thread only
                 cores = len(os.sched_getaffinity(0)) if hasattr(os, "sched_getaffinity") else (os.cpu_count() or 1)
                 stage_threads = 1 if len(devices) >= 4 else max(1, min(4, cores // (2 * len(devices))))
@@ -236,44 +289,28 @@ class ShardedFrontEnd:
             self.workers = [_worker_factory(d) for d in devices]
         self.devices = list(devices)
         self.B = int(frames_per_device)
-        self._queues = [queue.Queue() for _ in self.workers]
-        self._threads = [threading.Thread(target=self._loop, args=(i,), daemon=True) for i in range(len(self.workers))]
-        for t in self._threads:
-            t.start()
+        # workers without a native runner (the scheduling tests' stand-ins) get one Python thread each
+        self._native = all(hasattr(w, "launch") and hasattr(w, "finish") for w in self.workers)
+        self._queues, self._threads = [], []
+        if not self._native:
+            self._queues = [queue.Queue() for _ in self.workers]
+            self._threads = [threading.Thread(target=self._loop, args=(i,), daemon=True) for i in range(len(self.workers))]
+            for t in self._threads:
+                t.start()
 
     def _loop(self, i):
-        """Worker thread of GPU i.  With a two-phase worker (launch / finish) the staging copy of the next batch overlaps
-        the GPU work of the current one: a batch is finished -- its Future resolved -- only after the next one, if any is
-        queued, has been staged and enqueued."""
-        import queue
         w, q = self.workers[i], self._queues[i]
-        two_phase = hasattr(w, "launch") and hasattr(w, "finish")
-        pending = None                       # (future, token) of the batch running on the GPU
         while True:
-            try:
-                job = q.get(block=pending is None)
-            except queue.Empty:
-                job = False                  # nothing queued right now
-            nxt = None
-            if job not in (None, False):
-                fut, ids, frames = job
-                if fut.set_running_or_notify_cancel():
-                    try:
-                        if two_phase:
-                            nxt = (fut, w.launch(ids, frames))
-                        else:
-                            fut.set_result(w.run(ids, frames))
-                    except BaseException as exc:      # hand every failure to the waiter instead of killing the worker
-                        fut.set_exception(exc)
-            if pending is not None:
-                pfut, token = pending
-                try:
-                    pfut.set_result(w.finish(token))
-                except BaseException as exc:
-                    pfut.set_exception(exc)
-            pending = nxt
+            job = q.get()
             if job is None:
                 return
+            fut, ids, frames = job
+            if not fut.set_running_or_notify_cancel():
+                continue
+            try:
+                fut.set_result(w.run(ids, frames))
+            except BaseException as exc:      # hand every failure to the waiter instead of killing the worker
+                fut.set_exception(exc)
 
     def assignment(self, n_frames: int):
         """frame ids per worker for a batch of n_frames: b -> worker b mod G."""
@@ -283,15 +320,24 @@ class ShardedFrontEnd:
         return [list(range(i, n_frames, g)) for i in range(g)]
 
     def submit(self, frames):
-        """Deal the frames out; returns one Future per worker (None for a worker that got no frame)."""
+        """Deal the frames out; returns one future per worker (None for a worker that got no frame).  A frame that
+        cannot be accepted (dtype, shape, capacity) surfaces when that worker's future is asked for its result."""
         from concurrent.futures import Future
         futs = []
         for i, ids in enumerate(self.assignment(len(frames))):
             if not ids:
                 futs.append(None)
                 continue
-            fut = Future()
-            self._queues[i].put((fut, ids, [frames[b] for b in ids]))
+            mine = [frames[b] for b in ids]
+            if self._native:
+                fut = _NativeFuture(self.workers[i], None)
+                try:
+                    fut._token = self.workers[i].launch(ids, mine)
+                except BaseException as exc:
+                    fut._exc = exc
+            else:
+                fut = Future()
+                self._queues[i].put((fut, ids, mine))
             futs.append(fut)
         return futs
 

@@ -50,11 +50,12 @@ def parse_args():
     ap.add_argument("--e2e-eager", action="store_true", help="e2e arm: launch every copy / kernel eagerly instead of one graph per pipeline")
     ap.add_argument("--no-affinity", action="store_true",
                     help="do not pin the rank to the host cores NVML reports as local to its GPU (NUMA-local pinned buffers)")
-    ap.add_argument("--device-pipelines", type=int, default=2,
+    ap.add_argument("--device-pipelines", type=int, default=0,
                     help="device-resident arm: front ends (workspace + outputs + graph each) in flight, batches dealt round-robin; "
-                         "2 (default) lets the latency-bound voxelise chain of batch k+1 run under the HBM-bound canvas fill of batch "
-                         "k (+7 %% at 20 cm x 8, +11 %% at nuScenes x 8, neutral at 10 cm x 32); the strictly serial figure is always "
-                         "reported under 'serial'")
+                         "2 lets the latency-bound voxelise chain of batch k+1 run under the HBM-bound canvas fill of batch k (+7 %% "
+                         "at 20 cm x 8, +11 %% at nuScenes x 8, neutral at 10 cm x 32), 3 adds another 8 %% on canvases below 1 GB "
+                         "(nuScenes x 8); 0 (default) = 3 below 1 GB of canvas per batch, else 2; the strictly serial figure is "
+                         "always reported under 'serial'")
     ap.add_argument("--chain-priority", action="store_true",
                     help="capture the voxelise chain of every device pipeline on a high-priority stream (see PillarFrontEnd.capture)")
     ap.add_argument("--pipelines", type=int, default=3, help="e2e: independent stream/workspace sets in flight")
@@ -327,7 +328,7 @@ def run_b200(args, rank, world, local):
     counts = fe.voxel_num.cpu().numpy()
     bytes_alg = fe.bytes_algorithmic(n_points, counts)
 
-    d_dev = max(1, args.device_pipelines)
+    d_dev = args.device_pipelines if args.device_pipelines > 0 else (3 if 4 * 64 * cfg["_nx"] * cfg["_ny"] * B < 1e9 else 2)
     if d_dev > 1 and args.chain_priority:
         fe.capture(pts_d, offs_d, pillar, chain_priority=True)
     dpipes = [dict(fe=fe, stream=torch.cuda.Stream(dev))]

@@ -101,12 +101,32 @@ PF_API int pf_copy3(void *dst0, const void *src0, size_t bytes0, void *dst1, con
  * beyond n_frames empty) into `pinned_offsets`, host memory the caller then copies / captures to the device.
  *   kinds[b] = 0: frames[b] is pageable host memory -- copied into `pinned_stage` (same layout as device_points) by up to
  *                 `threads` host threads, then one asynchronous H2D;
- *   kinds[b] = 1: pinned host memory -- one asynchronous H2D straight from it;   kinds[b] = 2: device memory (D2D).
+ *   kinds[b] = 1: pinned host memory -- one asynchronous H2D straight from it;   kinds[b] = 2: device memory (D2D);
+ *   kinds[b] < 0: unknown -- the library asks the driver (cudaPointerGetAttributes).
  * rows[b] = points in frame b; row_bytes = bytes per point row.  One call per batch, so a Python worker thread holds the
  * interpreter lock for microseconds, not for the copies. */
 PF_API int pf_upload_frames(void *device_points, void *pinned_stage, const void *const *frames, const int64_t *rows,
                             const int32_t *kinds, int n_frames, int n_slots, int row_bytes, int threads,
                             int32_t *pinned_offsets, void *stream);
+
+/* Native per-GPU runner of the frame-sharded front end (the reference pins everything to cuda:0,
+ * train.py:27,190,276).  One host thread per runner; a ring of `n_slots` slots, each prepared once by the host language:
+ * device buffer for a batch of frames (frames_per_batch x capacity rows of row_bytes), pinned staging buffer of the same
+ * size (may be NULL if only pinned / device frames are submitted), pinned frame offsets (frames_per_batch + 1 int32), a
+ * stream, and an instantiated CUDA graph (cudaGraphExec_t) of the step that starts by copying those offsets to the device.
+ * pf_runner_submit enqueues one batch (pointers only; the frame memory must stay valid until pf_runner_wait returned) and
+ * returns a ticket >= 0 (or a negative pf_status); batches run in ticket order, ticket t in slot t % n_slots, i.e. the
+ * outputs of ticket t are overwritten when ticket t + n_slots runs.  pf_runner_wait blocks until the batch has left the GPU
+ * and reports its device time (upload + graph, ms; -1 if the slot was already reused).  kinds as in pf_upload_frames. */
+typedef struct pf_runner pf_runner;
+PF_API int pf_runner_create(int device, int n_slots, int frames_per_batch, int row_bytes, int stage_threads, pf_runner **out);
+PF_API int pf_runner_set_slot(pf_runner *r, int slot, void *graph_exec, void *stream, void *device_points,
+                              void *pinned_stage, int32_t *pinned_offsets);
+PF_API long long pf_runner_submit(pf_runner *r, const void *const *frames, const int64_t *rows, const int32_t *kinds,
+                                  int n_frames);
+PF_API int pf_runner_wait(pf_runner *r, long long ticket, float *device_ms);
+PF_API int pf_runner_destroy(pf_runner *r);
+PF_API const char *pf_runner_last_error(void);
 
 /* Diagnostics: with timing enabled every voxelise / fill call of this handle records a CUDA event after each of
  * its kernels (eager launches only -- do not capture such a call into a graph).  pf_debug_stage_times waits for

@@ -410,3 +410,28 @@ def test_sharded_front_end_matches_oracle(pf):
                     assert np.array_equal(_np(r.coors[rows])[:, :3], c)
                     want = oracle.scatter(stand_in[wi][rows], c, int(geom.grid_size[0]), int(geom.grid_size[1]))[0]
                     assert np.array_equal(_np(r.canvas[k]), want), f"frame {b} on GPU {r.device}"
+
+
+def test_overlong_frame_is_truncated_on_the_device(pf):
+    """the kernels read the frame length from the device-side offsets but the grids are sized from the host's
+    max_frame_points; a frame longer than that bound is processed up to the bound, deterministically, and the handle stays
+    usable (no stale counts, no stale cell ids)."""
+    cfg = cfgmod.builtin_config("20cm")
+    cfg["max_voxels"] = 5000
+    geom = cfgmod.derive_grid(cfg)
+    long_f = np.ascontiguousarray(synth.make_frame("S3", geom, 9000, 31), np.float32)
+    short_f = np.ascontiguousarray(synth.make_frame("S1", geom, 3000, 32, 300), np.float32)
+    fe = pf.PillarFrontEnd(cfg, max_batch=2, max_points_per_frame=9000, device=0)
+    pts = torch.from_numpy(np.concatenate([long_f, short_f])).cuda()
+    offs = torch.tensor([0, 9000, 12000], dtype=torch.int32).cuda()
+    pillar = torch.randn((2 * 5000, 64), device="cuda")
+    for bound, frames in ((4096, (long_f[:4096], short_f)), (9000, (long_f, short_f)), (2048, (long_f[:2048], short_f[:2048]))):
+        canvas = fe.step(pts, offs, pillar_feats=pillar, max_frame_points=bound)
+        counts = _np(fe.voxel_num)
+        for f, fr in enumerate(frames):
+            v, c, n = oracle.generate(geom, fr, 5000, 15)
+            assert counts[f] == len(n), f"bound {bound} frame {f}"
+            gv, gc, gn, _ = fe.frame_outputs(f, counts)
+            util.assert_vox_equal((_np(gv), _np(gc)[:, :3], _np(gn)), (v, c, n), f"bound {bound} frame {f}")
+            assert np.array_equal(_np(canvas[f]), oracle.scatter(_np(pillar[f * 5000: f * 5000 + len(n)]), c, fe.nx, fe.ny)[0])
+    fe.close()
