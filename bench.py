@@ -63,6 +63,7 @@ def parse_args():
                     help="raise --steps until the timed region lasts at least this long (BASELINE configs[4]: >= 2 s)")
     ap.add_argument("--pinned-frames", action="store_true",
                     help="--sharded: hand the frames over as pinned torch tensors (no host staging copy) instead of pageable numpy")
+    ap.add_argument("--stage-threads", type=int, default=0, help="--sharded: host threads per GPU for the pageable -> pinned copy (0 = the package's rule)")
     ap.add_argument("--sharded", action="store_true",
                     help="single-process mode: ONE process drives --gpus N GPUs through the package's ShardedFrontEnd "
                          "(one worker thread per GPU, numpy frames in, frame b -> GPU b mod N) instead of one rank per GPU")
@@ -621,7 +622,8 @@ def run_sharded(args):
     if args.pinned_frames:
         frames = [torch.from_numpy(f).pin_memory() for f in frames]
     K, W = args.steps, max(args.warmup, 3)
-    with pfm.ShardedFrontEnd(cfg, devices=G, frames_per_device=B, max_points_per_frame=cfg["frame_points"], depth=3) as sfe:
+    with pfm.ShardedFrontEnd(cfg, devices=G, frames_per_device=B, max_points_per_frame=cfg["frame_points"], depth=3,
+                             stage_threads=args.stage_threads or None) as sfe:
         for _ in range(W):
             sfe.run(frames)
         sampler = ClockSampler(sfe.devices[0])
