@@ -163,6 +163,10 @@ class VoxelGenerator:
         self._pool_F = None
         self._fused = {}        # (F, capacity, id(pfn)) -> _FusedPath (generate_and_scatter)
         self._threads = _stage_threads()
+        import threading
+        self._lock = threading.Lock()   # the reference's generate is a pure function and therefore thread-safe; this one owns
+                                        # buffers, so concurrent calls on ONE instance are serialised (use one instance per thread
+                                        # to run them side by side)
         self.voxel_time = 0.0   # kept for parity with InferData's timers (framework/dataset.py:208)
 
     # ------------------------------------------------------------------------------------------------
@@ -344,7 +348,8 @@ class VoxelGenerator:
         if kind == "torch" and not on_dev:
             points, kind = points.contiguous().numpy(), "numpy"
         if kind == "numpy":
-            (voxels, coors, num), v = self._generate_frame(points, n, n_feat, bool(device_outputs))
+            with self._lock:
+                (voxels, coors, num), v = self._generate_frame(points, n, n_feat, bool(device_outputs))
         else:                                          # CUDA tensor in: no staging, eager launch on the caller's stream
             dv, dc, dn, vnum = self._run([points.contiguous().to(_torch().device("cuda", self._device_index))],
                                          compact=False, coors_stride=3)
@@ -395,7 +400,8 @@ class VoxelGenerator:
                 self._fused.pop(old).close()
             fp = FusedFramePath(self, key[0], fold, n_channels)
             self._fused[key] = fp
-        return fp.run(points, n, self._threads)
+        with self._lock:
+            return fp.run(points, n, self._threads)
 
     def close(self):
         for h in self._handles.values():

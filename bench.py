@@ -378,6 +378,29 @@ def run_b200(args, rank, world, local):
     t_vox = float(np.mean([st[3 * i].elapsed_time(st[3 * i + 1]) for i in range(KS)])) * 1e-3
     t_scat = float(np.mean([st[3 * i + 1].elapsed_time(st[3 * i + 2]) for i in range(KS)])) * 1e-3
 
+    # the same fill launched back to back on its own (stand-alone pf_scatter on the batch's coordinates: k_map_index + the
+    # fill), for the reading of roofline.frac: inside the step a launch starts with the L2 full of the gather's dirty
+    # lines and has to write those back before its own bytes find room
+    fill_alone = None
+    if rank == 0:
+        cnts = fe.voxel_num.cpu().numpy()
+        rows = torch.cat([torch.arange(b * cfg["max_voxels"], b * cfg["max_voxels"] + int(cnts[b]), device=dev) for b in range(B)])
+        co_c, fe_c = fe.coors[rows].contiguous(), pillar[rows].contiguous()
+        sc_mod = pfm.PointPillarsScatter(B, geom.grid_size, 64)
+        with torch.no_grad():
+            for _ in range(3):
+                sc_mod(fe_c, co_c)
+            torch.cuda.synchronize(dev)
+            f0, f1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            n_fa = 20
+            f0.record()
+            for _ in range(n_fa):
+                sc_mod(fe_c, co_c)
+            f1.record()
+            torch.cuda.synchronize(dev)
+        fill_alone = f0.elapsed_time(f1) / n_fa * 1e-3
+        del sc_mod, co_c, fe_c, rows
+
     # ---------------- next-row N1: the learned PFN in the loop, fused vs torch (reported beside, not the headline) ----
     with_pfn = None
     if not args.no_pfn:
@@ -601,7 +624,7 @@ def run_b200(args, rank, world, local):
         dist.destroy_process_group()
     fill_variant = int(importlib.import_module("3d_object_detection_b200._lib").load().pf_debug_set_fill_variant(
         int(os.environ["PF_FILL_VARIANT"]) if os.environ.get("PF_FILL_VARIANT", "").isdigit() else -1))
-    return dict(fill_variant=fill_variant, cfg=cfg, geom=geom, frames=frames, B=B, K=K, W=W, t_dev=t_dev, t_e2e=t_e2e, t_vox=t_vox,
+    return dict(fill_alone=fill_alone, fill_variant=fill_variant, cfg=cfg, geom=geom, frames=frames, B=B, K=K, W=W, t_dev=t_dev, t_e2e=t_e2e, t_vox=t_vox,
                 t_scat=t_scat, with_pfn=with_pfn, anchor=anchor, post=post, single=single, bound=bound, w_e2e=w_e2e, t_serial=t_serial, d_dev=d_dev, counts=counts, bytes_alg=bytes_alg, n_points=n_points, tot_pts=tot_pts,
                 tot_frames=tot_frames, clocks=clocks, h2d=h2d, d2h=d2h, fe=fe, depth=depth, world=world)
 
@@ -740,7 +763,12 @@ def main():
         "roofline": {"kernel": "k_canvas_fill<1,1,8> (pf_scatter_from_map, 32-byte streaming stores)", "bound": "hbm", "achieved": achieved,
                      "peak": peak, "unit": "GB/s", "frac": achieved / peak, "traffic": ncu_traffic(args.grid, B),
                      "peak_source": peak_src, "frac_of_nominal_8TBs": achieved / 8000.0,
-                     "bytes_per_launch": scat_bytes, "ms_per_launch": 1e3 * r["t_scat"]},
+                     "bytes_per_launch": scat_bytes, "ms_per_launch": 1e3 * r["t_scat"],
+                     "back_to_back": None if not r["fill_alone"] else {
+                         "ms_per_launch": 1e3 * r["fill_alone"], "frac": scat_bytes / r["fill_alone"] / 1e9 / peak,
+                         "note": "the same canvas through the stand-alone pf_scatter (k_map_index + the same fill kernel, fresh canvas "
+                                 "allocation included), 20 launches back to back: no gather in front, so the L2 does not start full of "
+                                 "another kernel's dirty lines"}},
     }
     link = host_link_ceiling(r["world"])
     if link is not None:
