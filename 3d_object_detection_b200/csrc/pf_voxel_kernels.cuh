@@ -95,11 +95,6 @@ __global__ void __launch_bounds__(256) k_quantize(Params p, Work w, const float 
 // max_voxels publishes the cut-off index i* (the reference's `break`).
 // Tiles are numbered by a per-frame ticket in CTA start order: the look-back waits only on tiles with a lower
 // ticket, i.e. on CTAs that are already running, whatever order the hardware dispatches blockIdx in.
-__device__ __forceinline__ unsigned ld_status(const int32_t *p)
-{
-    return *reinterpret_cast<const volatile unsigned *>(p);
-}
-
 #ifndef PF_ASSIGN_TILE
 #define PF_ASSIGN_TILE 4096   // points per k_assign CTA (its own tiling; k_tile_rank keeps kTile).  Measured 2048 /
                               // 4096 / 8192: 19.5 / 16.1 / 18.6 us (20 cm), 29.4 / 22.5 / 22.8 (nuScenes), 82.5 / 72.5 / 72.1 (10 cm)
@@ -165,7 +160,7 @@ __global__ void __launch_bounds__(256) k_assign(Params p, Work w, const int32_t 
     if (warp == 0) {
         // publish this tile's total first so that no successor ever waits on our own look-back
         if (lane == 0)
-            *reinterpret_cast<volatile unsigned *>(status + t) = ((t == 0 ? 2u : 1u) << 30) | (unsigned)block_total;
+            st_flag(status + t, (int)(((t == 0 ? 2u : 1u) << 30) | (unsigned)block_total));
         int base = 0;
         if (t > 0) {
             int j = t - 1 - lane;   // lane 0 looks at the nearest predecessor
@@ -174,7 +169,7 @@ __global__ void __launch_bounds__(256) k_assign(Params p, Work w, const int32_t 
                 unsigned st = 2u << 30;   // "before tile 0": inclusive prefix 0
                 if (j >= 0) {
                     // back off between polls: hundreds of warps spin on the lines their predecessors must write
-                    while (((st = ld_status(status + j)) >> 30) == 0u) __nanosleep(50);
+                    while (((st = (unsigned)ld_flag(status + j)) >> 30) == 0u) __nanosleep(50);
                 }
                 const unsigned inc_mask = __ballot_sync(0xffffffffu, (st >> 30) == 2u);
                 int val = (int)(st & 0x3fffffffu);
@@ -188,7 +183,7 @@ __global__ void __launch_bounds__(256) k_assign(Params p, Work w, const int32_t 
                 base += val;
                 j -= 32;
             }
-            if (lane == 0) *reinterpret_cast<volatile unsigned *>(status + t) = (2u << 30) | (unsigned)(base + block_total);
+            if (lane == 0) st_flag(status + t, (int)((2u << 30) | (unsigned)(base + block_total)));
         }
         if (lane == 0) s_base = base;
     }
