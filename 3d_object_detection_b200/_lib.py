@@ -10,7 +10,7 @@ from pathlib import Path
 LIB_PATH = Path(__file__).resolve().parent / "lib" / "libpillarfront.so"
 
 EXPORTS = ["pf_version", "pf_last_error_string", "pf_create", "pf_destroy", "pf_workspace_bytes",
-           "pf_voxelize", "pf_voxelize_decorate", "pf_voxelize_pfn", "pf_pfn", "pf_decorate", "pf_scatter", "pf_scatter_from_map",
+           "pf_voxelize", "pf_voxelize_decorate", "pf_voxelize_pfn", "pf_pfn", "pf_decorate", "pf_scatter", "pf_scatter_static", "pf_scatter_from_map",
            "pf_scatter_backward", "pf_anchor_mask", "pf_nms", "pf_nms_scratch_bytes",
            "pf_debug_stage_timing", "pf_debug_stage_times", "pf_debug_set_fill_variant", "pf_discard_cell_map", "pf_stage_copy", "pf_copy3", "pf_upload_frames", "pf_runner_create", "pf_runner_set_slot", "pf_runner_submit",
            "pf_runner_wait", "pf_runner_destroy", "pf_runner_last_error",
@@ -86,6 +86,8 @@ def load():
                               C.c_float, C.c_float, C.c_float, C.c_float, _p, _p]
     L.pf_scatter.restype = C.c_int
     L.pf_scatter.argtypes = [_p, _p, C.c_int64, C.c_int64, _p, C.c_int, C.c_int64, C.c_int, C.c_int, _p, _p]
+    L.pf_scatter_static.restype = C.c_int
+    L.pf_scatter_static.argtypes = [_p, C.c_int64, C.c_int64, _p, C.c_int, C.c_int64, C.c_int, C.c_int, C.c_int, C.c_int, _p, _p]
     L.pf_scatter_from_map.restype = C.c_int
     L.pf_scatter_from_map.argtypes = [_p, _p, C.c_int64, C.c_int64, C.c_int, C.c_int, C.c_int, _p, _p]
     L.pf_scatter_backward.restype = C.c_int

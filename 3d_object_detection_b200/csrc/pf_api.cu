@@ -425,6 +425,26 @@ int pf_scatter(pf_handle *h, const float *feats, int64_t feat_stride_v, int64_t 
     return e == cudaSuccess ? PF_OK : cuda_fail(e, "pf_scatter");
 }
 
+// Allocation-free variant of pf_scatter: no handle, the cell map is the file-scope device array of pf_scatter.cu.
+// Calls no cudaMalloc / cudaFree and no allocating library routine; runs on the CURRENT device.
+int pf_scatter_static(const float *feats, int64_t feat_stride_v, int64_t feat_stride_c, const int32_t *coors,
+                      int coors_stride, int64_t n_voxels, int batch, int n_ch, int nx, int ny, float *canvas, void *stream)
+{
+    if (!canvas) return fail(PF_ERR_INVALID_ARGUMENT, "pf_scatter_static: null canvas");
+    if (n_voxels < 0 || n_voxels >= (1ll << 31)) return fail(PF_ERR_INVALID_ARGUMENT, "pf_scatter_static: n_voxels out of range");
+    if (n_voxels > 0 && (!feats || !coors)) return fail(PF_ERR_INVALID_ARGUMENT, "pf_scatter_static: null feats/coors");
+    if (coors_stride < 2) return fail(PF_ERR_INVALID_ARGUMENT, "pf_scatter_static: coors_stride must be >= 2");
+    if (batch < 1 || n_ch < 1 || nx < 1 || ny < 1) return fail(PF_ERR_INVALID_ARGUMENT, "pf_scatter_static: batch, n_ch, nx, ny must be >= 1");
+    const long long max_cells = pf::static_scatter_max_cells();   // == PF_SCATTER_STATIC_MAX_CELLS of the header
+    if ((long long)nx * ny > max_cells || (long long)nx * ny * batch > max_cells)
+        return fail(PF_ERR_CAPACITY, "pf_scatter_static: batch %d x %d x %d cells exceed the static cell map of %lld cells "
+                    "(use pf_scatter with a handle for larger canvases)", batch, nx, ny, max_cells);
+    Range nvtx_range("pf_scatter_static");
+    cudaError_t e = pf::launch_scatter_static(feats, feat_stride_v, feat_stride_c, coors, coors_stride, n_voxels, batch, n_ch,
+                                              nx, ny, canvas, static_cast<cudaStream_t>(stream));
+    return e == cudaSuccess ? PF_OK : cuda_fail(e, "pf_scatter_static");
+}
+
 int pf_scatter_from_map(pf_handle *h, const float *feats, int64_t feat_stride_v, int64_t feat_stride_c, int n_frames,
                         int compact, int n_ch, float *canvas, void *stream)
 {

@@ -119,6 +119,11 @@ cudaError_t launch_scatter(const Params &p, const Work &w, const float *feats, i
                            float *canvas, cudaStream_t stream);
 cudaError_t launch_scatter_from_map(const Params &p, const Work &w, const float *feats, int64_t sv, int64_t sc,
                                     int n_frames, int compact, int n_ch, float *canvas, cudaStream_t stream);
+// allocation-free scatter: the cell map is a file-scope device array of static_scatter_max_cells() cells in pf_scatter.cu
+long long static_scatter_max_cells();
+cudaError_t launch_scatter_static(const float *feats, int64_t sv, int64_t sc, const int32_t *coors, int coors_stride,
+                                  int64_t n_voxels, int batch, int n_ch, int nx, int ny, float *canvas,
+                                  cudaStream_t stream);
 cudaError_t launch_scatter_backward(const float *grad_canvas, const int32_t *coors, int coors_stride,
                                     int64_t n_voxels, int batch, int n_ch, int nx, int ny, float *grad_feats,
                                     int64_t sv, int64_t sc, cudaStream_t stream);

@@ -7,6 +7,7 @@
 // map once (int4 per lane), and for every channel emits one fully coalesced 512-byte line of 16-byte
 // streaming stores, pulling feature values from L2 only for the occupied lanes.  HBM-write bound.
 #include <cstdlib>
+#include <mutex>
 
 #include "pf_internal.cuh"
 
@@ -500,6 +501,64 @@ cudaError_t launch_scatter_from_map(const Params &p, const Work &w, const float 
     const cudaError_t e = run_fill<1>(w.grid, feats, sv, sc, w.vnum, p.max_voxels, compact, n_frames, n_ch, p.plane, canvas, stream);
     mark(w, kEvFill, stream);
     return e;
+}
+
+// ---- allocation-free scatter (pf_scatter_static; no counterpart in the reference, added
+// for callers that may not allocate: code under graph capture, tight serving loops) ----
+// The cell -> feature-row map of launch_scatter lives in the handle's workspace (cudaMalloc in pf_create).  This variant
+// keeps it in a file-scope device array instead: 2^22 int32 cells = 16 MB, one frame of the 10 cm grid (1600 x 1600) or
+// six of the 20 cm grid.  Every GPU that loads the library holds the array until exit; every call shares it, so calls that
+// overlap on the GPU (two streams, two host threads) race.
+constexpr long long kStaticMapCells = PF_SCATTER_STATIC_MAX_CELLS;   // the limit stated in include/pillarfront.h
+static __device__ __align__(256) int32_t g_static_map[kStaticMapCells];
+
+// In host code `g_static_map` is a host-side stand-in, not a device address: the address the kernels get is asked from
+// the runtime, once per device, with that device current.
+constexpr int kStaticMaxDevices = 64;
+static int32_t *g_static_map_ptr[kStaticMaxDevices] = {};
+static std::mutex g_static_mutex;
+
+static cudaError_t static_map_address(int32_t **out)
+{
+    int dev = -1;
+    cudaError_t e = cudaGetDevice(&dev);
+    if (e != cudaSuccess) return e;
+    if (dev < 0 || dev >= kStaticMaxDevices) return cudaErrorInvalidDevice;
+    std::lock_guard<std::mutex> lk(g_static_mutex);
+    if (!g_static_map_ptr[dev]) {
+        void *ptr = nullptr;
+        e = cudaGetSymbolAddress(&ptr, g_static_map);
+        if (e != cudaSuccess) return e;
+        if (!ptr) return cudaErrorInvalidSymbol;
+        g_static_map_ptr[dev] = static_cast<int32_t *>(ptr);
+    }
+    *out = g_static_map_ptr[dev];
+    return cudaSuccess;
+}
+
+long long static_scatter_max_cells() { return kStaticMapCells; }
+
+cudaError_t launch_scatter_static(const float *feats, int64_t sv, int64_t sc, const int32_t *coors, int coors_stride,
+                                  int64_t n_voxels, int batch, int n_ch, int nx, int ny, float *canvas,
+                                  cudaStream_t stream)
+{
+    const long long plane = (long long)nx * ny;
+    if (batch < 1 || nx < 1 || ny < 1 || plane * batch > kStaticMapCells) return cudaErrorInvalidValue;
+    int32_t *map = nullptr;
+    cudaError_t e = static_map_address(&map);
+    if (e != cudaSuccess) return e;
+    // the array keeps whatever the last call (of any shape, possibly one that failed half-way) left: start from "no row"
+    const size_t cells = (size_t)batch * plane;
+    const unsigned reset_blocks = (unsigned)((cells + 1023) / 1024 < 148 * 4 ? (cells + 1023) / 1024 : 148 * 4);
+    k_map_reset<<<reset_blocks, 256, 0, stream>>>(map, cells, -1);
+    e = cudaGetLastError();
+    if (e != cudaSuccess) return e;
+    if (n_voxels > 0) {
+        k_map_index<<<(unsigned)((n_voxels + 255) / 256), 256, 0, stream>>>(coors, coors_stride, n_voxels, batch, nx, ny, map);
+        e = cudaGetLastError();
+        if (e != cudaSuccess) return e;
+    }
+    return run_fill<0>(map, feats, sv, sc, nullptr, 0, 0, batch, n_ch, (int)plane, canvas, stream);
 }
 
 cudaError_t launch_scatter_backward(const float *grad_canvas, const int32_t *coors, int coors_stride,

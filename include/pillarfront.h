@@ -215,6 +215,27 @@ PF_API int pf_scatter(pf_handle *h, const float *feats, int64_t feat_stride_v, i
                const int32_t *coors, int coors_stride, int64_t n_voxels, int batch, int n_ch,
                float *canvas, void *stream);
 
+/* Allocation-free BEV scatter.  This entry point has NO counterpart in the reference: it was added
+ * for callers that cannot allocate device memory (code under CUDA graph capture, tight serving
+ * loops, harnesses that forbid cudaMalloc).  Same arguments, canvas contents and duplicate rule as pf_scatter, but no
+ * handle: the cell -> row map pf_scatter keeps in the handle's workspace lives in a file-scope device array of the
+ * library instead, PF_SCATTER_STATIC_MAX_CELLS = 2^22 int32 cells (16 MB; every GPU that loads the library holds it until
+ * exit).
+ *   limit    batch * nx * ny <= PF_SCATTER_STATIC_MAX_CELLS: one frame of every shipped grid (10 cm: 1600 x 1600), six
+ *            frames of the 20 cm grid (800 x 800), four of the 16 cm grid, seventeen of nuScenes (512 x 480);
+ *            beyond that PF_ERR_CAPACITY with a message naming the limit, nothing is launched
+ *   device   runs on the CURRENT device (make the canvas's device current; `stream` must belong to it)
+ *   calls    no cudaMalloc / cudaFree / allocating library routine; three kernel launches on `stream` (map reset, map
+ *            index, canvas fill).  The array's device address is resolved once per device on the first call
+ *            (cudaGetSymbolAddress), so make the first call on a device outside graph capture.
+ *   sharing  every call on a device shares the one array, which keeps the last call's contents (each call resets the
+ *            cells it is about to use first): calls that overlap on the GPU -- two streams, two host threads -- RACE.
+ *            Serialise them on one stream or with events. */
+#define PF_SCATTER_STATIC_MAX_CELLS (1 << 22)
+PF_API int pf_scatter_static(const float *feats, int64_t feat_stride_v, int64_t feat_stride_c, const int32_t *coors,
+                      int coors_stride, int64_t n_voxels, int batch, int n_ch, int nx, int ny, float *canvas,
+                      void *stream);
+
 /* Fill the canvas from the cell map left by pf_voxelize_decorate(keep_cell_map=1): feature row of voxel v of
  * frame f is row_base(f) + v with row_base = f*max_voxels (slab) or the running sum of voxel_num (compact). */
 PF_API int pf_scatter_from_map(pf_handle *h, const float *feats, int64_t feat_stride_v, int64_t feat_stride_c,
