@@ -84,9 +84,11 @@ __device__ __forceinline__ bool overlaps(const float4 a, const float4 b, double 
     const double width = fmax((double)dw + 1.0, 0.0);
     const double height = fmax((double)dh + 1.0, 0.0);
     const double inter = __dmul_rn(width, height);
-    const double sa = __dmul_rn((double)__fsub_rn(a.z, a.x) + 1.0, (double)__fsub_rn(a.w, a.y) + 1.0);
+    // Sa + Sb the way numba / NVVM compile the reference's source (tests/golden/nms_iou_ptx_ops.json): Sb rounded, Sa's
+    // product contracted into the sum -- fma.rn.f64(aw, ah, Sb) -- with a = the earlier (row) box
     const double sb = __dmul_rn((double)__fsub_rn(b.z, b.x) + 1.0, (double)__fsub_rn(b.w, b.y) + 1.0);
-    return __ddiv_rn(inter, __dsub_rn(__dadd_rn(sa, sb), inter)) > thresh;
+    const double sab = __fma_rn((double)__fsub_rn(a.z, a.x) + 1.0, (double)__fsub_rn(a.w, a.y) + 1.0, sb);
+    return __ddiv_rn(inter, __dsub_rn(sab, inter)) > thresh;
 }
 
 // mask[seg][i][cb]: bit t set <=> sorted box i overlaps sorted box cb*64 + t (only cb >= i/64, and t > i%64 on the

@@ -48,6 +48,8 @@ def lib():
                                             C.c_int32, C.c_int32, C.c_float, C.c_float, C.c_float,
                                             C.c_float, _f32p, C.c_int32, _f32p, _i32p, _i32p, _i32p,
                                             _f32p, _f32p, C.c_int32]
+        L.oracle_nms_iou.restype = None
+        L.oracle_nms_iou.argtypes = [_f32p, C.c_int32, np.ctypeslib.ndpointer(dtype=np.float64, flags="C_CONTIGUOUS")]
         _LIB = L
     return _LIB
 
@@ -236,20 +238,16 @@ def anchors_mask(coors, shape, anchor_coors):
 
 
 def nms_iou_matrix(boxes):
-    """iou_device, framework/nms.py:102-113, for all pairs, in the precision compiled numba gives it: the box edges
-    are float32, `right - left` is a float32 subtraction, and `+ 1` (an int64 literal) promotes everything after it
-    to float64 (numba typing: float32 + int64 -> float64)."""
-    b = np.asarray(boxes, np.float32)
-    x0, y0, x1, y1 = b[:, 0], b[:, 1], b[:, 2], b[:, 3]
-    left = np.maximum(x0[:, None], x0[None, :])
-    right = np.minimum(x1[:, None], x1[None, :])
-    top = np.maximum(y0[:, None], y0[None, :])
-    bottom = np.minimum(y1[:, None], y1[None, :])
-    width = np.maximum((right - left).astype(np.float64) + 1, 0.0)
-    height = np.maximum((bottom - top).astype(np.float64) + 1, 0.0)
-    inter = width * height
-    area = ((x1 - x0).astype(np.float64) + 1) * ((y1 - y0).astype(np.float64) + 1)
-    return inter / (area[:, None] + area[None, :] - inter)
+    """iou_device(a = row box, b = column box), framework/nms.py:102-113, for all pairs, in the arithmetic compiled numba
+    gives it (oracle_nms_iou in pillar_oracle.c; PTX evidence tests/golden/nms_iou_ptx_ops.json): the box edges are float32,
+    `right - left` is a float32 subtraction, `+ 1` (an int64 literal) promotes everything after it to float64 (numba typing:
+    float32 + int64 -> float64), and Sa + Sb is one fma."""
+    b = np.ascontiguousarray(np.asarray(boxes, np.float32)[:, :4])
+    n = b.shape[0]
+    out = np.empty((n, n), np.float64)
+    if n:
+        lib().oracle_nms_iou(b.reshape(-1), n, out.reshape(-1))
+    return out
 
 
 def nms_gpu(dets, nms_overlap_thresh):

@@ -17,6 +17,8 @@
  *   oracle_scatter           <- networks/pointpillars8_shared.py:76-111 (PointPillarsScatter.forward, B = 1
  *                               index rule x*ny + y applied per batch item; see DESIGN.md on F10)
  *   oracle_scatter_cmajor    <- networks/pointpillars8_export.py:44-51 (Scatter.run, channel-major features)
+ *   oracle_nms_iou           <- framework/nms.py:102-113 (iou_device) in the arithmetic numba's CUDA target compiles
+ *                               it to (tests/golden/nms_iou_ptx_ops.json, oracle/make_golden_nms_f64.py)
  *
  * Build: gcc -O2 -ffp-contract=off -fopenmp -shared -fPIC (oracle/build.py).
  */
@@ -204,4 +206,29 @@ int64_t oracle_frontend_batch(const float *points, const int64_t *frame_offsets,
         total += v;
     }
     return failed ? -1 : total;
+}
+
+/* iou_device(a = box i, b = box j) for all pairs, framework/nms.py:102-113, instruction for instruction as numba 0.65 /
+ * NVVM compile the reference's source for the GPU (PTX kept by oracle/make_golden_nms_f64.py): min / max and the edge
+ * differences in float32, cvt to float64, `+ 1`, max(., 0), products and the quotient in float64, and ONE contraction --
+ * Sa + Sb is fma(aw, ah, Sb) with Sb = bw * bh rounded, so the result is not symmetric in (a, b) at the last bit when a
+ * product is inexact.  The kernel calls it with a = the earlier (higher-scored) box (nms.py:139-140). */
+void oracle_nms_iou(const float *boxes, int32_t n, double *iou)
+{
+#pragma omp parallel for schedule(static)
+    for (int32_t i = 0; i < n; ++i) {
+        const float *a = boxes + 4 * (int64_t)i;
+        const double aw = (double)(a[2] - a[0]) + 1.0, ah = (double)(a[3] - a[1]) + 1.0;
+        for (int32_t j = 0; j < n; ++j) {
+            const float *b = boxes + 4 * (int64_t)j;
+            const float left = fmaxf(a[0], b[0]), right = fminf(a[2], b[2]);
+            const float top = fmaxf(a[1], b[1]), bottom = fminf(a[3], b[3]);
+            const double width = fmax((double)(right - left) + 1.0, 0.0);
+            const double height = fmax((double)(bottom - top) + 1.0, 0.0);
+            const double inter = width * height;
+            const double sb = ((double)(b[2] - b[0]) + 1.0) * ((double)(b[3] - b[1]) + 1.0);
+            const double sab = fma(aw, ah, sb);
+            iou[(int64_t)i * n + j] = inter / (sab - inter);
+        }
+    }
 }

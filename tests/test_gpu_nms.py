@@ -34,6 +34,21 @@ def test_matches_reference_golden(pf, name):
     assert got_t.is_cuda and got_t.dtype == torch.int64 and got_t.cpu().tolist() == want[:300]
 
 
+@pytest.mark.parametrize("name", ["t01", "t05", "t03"])
+def test_float64_rule_matches_compiled_numba(pf, name):
+    """Decisive pairs within a few float32 ulps of the threshold (and one exact tie): the keep list of the reference's
+    nms_gpu with iou_device compiled by real numba (oracle/make_golden_nms_f64.py; float32 edge differences, `+ 1` and
+    the quotient in float64, float64 `>`).  An all-float32 overlap test would return `keep_if_float32` instead."""
+    z = np.load(util.GOLD / "nms_f64.npz")
+    dets, thresh = z[f"{name}_dets"], float(z[f"{name}_thresh"])
+    want, f32 = z[f"{name}_keep"].tolist(), z[f"{name}_keep_if_float32"].tolist()
+    m = _nms(pf)
+    got = m.nms_gpu(dets, thresh)
+    assert got != f32, "the device evaluates the overlap in float32"
+    assert got == want
+    assert m.nms_gpu(torch.from_numpy(dets).cuda(), thresh) == want
+
+
 @pytest.mark.parametrize("n,thresh,seed", [(1000, 0.1, 1), (1000, 0.5, 2), (1023, 0.3, 3), (1025, 0.1, 4), (2500, 0.1, 5),
                                            (4096, 0.7, 6), (129, 0.0, 7), (333, 0.99, 8)])
 def test_matches_oracle_at_size(pf, n, thresh, seed):

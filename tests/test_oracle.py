@@ -220,6 +220,30 @@ def test_nms_oracle_matches_reference_golden(name):
     assert oracle.nms(dets[:0, :4], dets[:0, 4], 1000, 300, thresh) is None
 
 
+@pytest.mark.parametrize("name", ["t01", "t05", "t03"])
+def test_nms_oracle_float64_rule_matches_compiled_numba(name):
+    """The PRECISION of the overlap test: decisive pairs within a few float32 ulps of the threshold, expected keep list
+    from the reference's own nms_gpu with its iou_device compiled by real numba (oracle/make_golden_nms_f64.py); an
+    all-float32 evaluation gives `keep_if_float32`, which differs in every decisive pair."""
+    z = np.load(util.GOLD / "nms_f64.npz")
+    dets, thresh = z[f"{name}_dets"], z[f"{name}_thresh"]
+    want, f32 = z[f"{name}_keep"].tolist(), z[f"{name}_keep_if_float32"].tolist()
+    assert want != f32
+    assert oracle.nms_gpu(dets, thresh) == want
+
+
+def test_nms_ptx_evidence_of_the_reference_kernel():
+    """What numba's CUDA target makes of the reference's iou_device / nms_kernel source (committed by the generator):
+    float32 edge differences, everything from the `+ 1` on in float64, float64 comparison with the threshold."""
+    import json
+    ev = json.loads((util.GOLD / "nms_iou_ptx_ops.json").read_text())
+    assert ev["numba_return_type"] == "float64"
+    assert {"sub.f32", "cvt.f64.f32", "add.f64", "mul.f64", "div.rn.f64"} <= set(ev["float_ptx_ops"])
+    assert not any(op.endswith(".f32") and op.split(".")[0] in ("div", "mul", "add") for op in ev["float_ptx_ops"])
+    assert "setp.gt.f64" in ev["kernel_float_ptx_ops"]
+    assert not any(op.startswith("setp") and op.endswith("f32") for op in ev["kernel_float_ptx_ops"])
+
+
 # ---- detection post-processing (row N4 around the NMS) ---------------------------------------------------------------
 
 POST_CASES = util.POST_CASES
