@@ -12,7 +12,7 @@ LIB_PATH = Path(__file__).resolve().parent / "lib" / "libpillarfront.so"
 EXPORTS = ["pf_version", "pf_last_error_string", "pf_create", "pf_destroy", "pf_workspace_bytes",
            "pf_voxelize", "pf_voxelize_decorate", "pf_voxelize_pfn", "pf_pfn", "pf_decorate", "pf_scatter", "pf_scatter_static", "pf_scatter_from_map",
            "pf_scatter_backward", "pf_anchor_mask", "pf_nms", "pf_nms_scratch_bytes",
-           "pf_debug_stage_timing", "pf_debug_stage_times", "pf_debug_set_fill_variant", "pf_discard_cell_map", "pf_stage_copy", "pf_copy3", "pf_upload_frames", "pf_runner_create", "pf_runner_set_slot", "pf_runner_submit",
+           "pf_debug_stage_timing", "pf_debug_stage_times", "pf_debug_set_fill_variant", "pf_debug_set_pdl", "pf_discard_cell_map", "pf_stage_copy", "pf_copy3", "pf_upload_frames", "pf_runner_create", "pf_runner_set_slot", "pf_runner_submit",
            "pf_runner_wait", "pf_runner_destroy", "pf_runner_last_error",
            "pf_postprocess", "pf_post_scratch_bytes", "pf_post_scratch_layout"]
 
@@ -120,6 +120,8 @@ def load():
     L.pf_copy3.argtypes = [_p, _p, C.c_size_t, _p, _p, C.c_size_t, _p, _p, C.c_size_t, _p]
     L.pf_debug_set_fill_variant.restype = C.c_int
     L.pf_debug_set_fill_variant.argtypes = [C.c_int]
+    L.pf_debug_set_pdl.restype = C.c_int
+    L.pf_debug_set_pdl.argtypes = [C.c_int]
     L.pf_discard_cell_map.restype = C.c_int
     L.pf_discard_cell_map.argtypes = [_p, _p]
     L.pf_nms_scratch_bytes.restype = C.c_size_t

@@ -288,6 +288,12 @@ int pf_debug_set_fill_variant(int variant)
     return pf::fill_variant();
 }
 
+int pf_debug_set_pdl(int enable)
+{
+    pf::set_pdl(enable);
+    return pf::pdl_enabled() ? 1 : 0;
+}
+
 int pf_debug_stage_times(pf_handle *h, float *ms, int capacity)
 {
     if (!h || !ms) return fail(PF_ERR_INVALID_ARGUMENT, "pf_debug_stage_times: null argument");

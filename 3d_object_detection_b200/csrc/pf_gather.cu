@@ -31,6 +31,8 @@ __global__ void __launch_bounds__(kG4Warps * 32) k_gather4(Params p, Work w, Gat
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     const int g = lane / GROUP, gl = lane % GROUP;
     const int f = FROM_POINTS ? blockIdx.y : 0;
+    pdl_trigger();
+    pdl_wait();   // last kernel of the voxelise chain: nothing to do before k_slot's lists exist (no-op when launched plainly)
     const int n_vox = FROM_POINTS ? w.vnum[f] : (int)a.n_voxels;
     const int v0 = (blockIdx.x * kG4Warps + warp) * VPW;   // first voxel of this warp
     if (v0 >= n_vox) return;
@@ -224,6 +226,7 @@ template <int GROUP, int PT, bool FROM_POINTS, bool PFN>
 static cudaError_t run_g4x(const Params &p, const Work &w, const GatherArgs &a, long long voxels, int n_frames,
                            cudaStream_t stream)
 {
+    const bool dependent = FROM_POINTS && pdl_stage(5) && !w.ev;   // behind k_slot on the same stream
     constexpr int VPW = 32 / GROUP;
     const size_t smem = (size_t)kG4Warps * g4_warp_floats(VPW, p.P) * sizeof(float);
     if (smem > 48 * 1024) {
@@ -233,8 +236,7 @@ static cudaError_t run_g4x(const Params &p, const Work &w, const GatherArgs &a, 
     }
     const long long per_cta = (long long)kG4Warps * VPW;
     const dim3 grid((unsigned)((voxels + per_cta - 1) / per_cta), (unsigned)n_frames);
-    k_gather4<GROUP, PT, FROM_POINTS, PFN><<<grid, kG4Warps * 32, smem, stream>>>(p, w, a);
-    return cudaGetLastError();
+    return launch_k(k_gather4<GROUP, PT, FROM_POINTS, PFN>, grid, dim3(kG4Warps * 32), smem, stream, dependent, p, w, a);
 }
 
 template <int GROUP, int PT, bool FROM_POINTS>

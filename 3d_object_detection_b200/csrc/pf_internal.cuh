@@ -133,6 +133,25 @@ cudaError_t launch_anchor_mask(const int32_t *coors, int coors_stride, const int
                                cudaStream_t stream);
 
 size_t gather_smem_needed(int P, int F);   // pf_voxelize.cu
+bool pdl_enabled();            // pf_voxelize.cu: launch the chain kernels as programmatic dependents (PF_PDL / pf_debug_set_pdl)
+void set_pdl(int on);
+bool pdl_stage(int bit);   // experiments: PF_PDL_MASK selects which launches are dependents
+
+#if defined(__CUDACC__)
+// kernel launch with or without the programmatic-dependent-launch attribute
+template <class... KArgs, class... Args>
+inline cudaError_t launch_k(void (*kern)(KArgs...), dim3 grid, dim3 block, size_t smem, cudaStream_t stream, bool dependent,
+                            Args... args)
+{
+    cudaLaunchConfig_t cfg{};
+    cfg.gridDim = grid, cfg.blockDim = block, cfg.dynamicSmemBytes = smem, cfg.stream = stream;
+    cudaLaunchAttribute attr{};
+    attr.id = cudaLaunchAttributeProgrammaticStreamSerialization;
+    attr.val.programmaticStreamSerializationAllowed = 1;
+    cfg.attrs = &attr, cfg.numAttrs = dependent ? 1 : 0;
+    return cudaLaunchKernelEx(&cfg, kern, static_cast<KArgs>(args)...);
+}
+#endif
 int fill_variant();            // pf_scatter.cu: which canvas-fill kernel runs (see pf_debug_set_fill_variant)
 void set_fill_variant(int v);
 
@@ -196,6 +215,20 @@ __device__ __forceinline__ void st_cs_f4(float *ptr, float a, float b, float c, 
     asm volatile("st.global.cs.v4.f32 [%0], {%1, %2, %3, %4};" ::"l"(ptr), "f"(a), "f"(b), "f"(c), "f"(d)
                  : "memory");
 }
+#endif
+
+// Programmatic dependent launch (sm_90+): a kernel launched with the programmatic-stream-serialization attribute may be
+// scheduled as soon as every CTA of the kernel in front of it on the stream has executed pdl_trigger() (or exited); it
+// runs its prologue (index arithmetic, shared-memory clears, loads of CALLER inputs) under the predecessor's tail and
+// stops at pdl_wait() until the predecessor grid has completed and its writes are visible.  Rules used in this library:
+// every chain kernel triggers first thing, and touches nothing an earlier chain kernel writes before its pdl_wait().
+// Without the launch attribute both instructions are no-ops.
+#ifdef PF_HOST_EMUL
+inline void pdl_wait() {}
+inline void pdl_trigger() {}
+#else
+__device__ __forceinline__ void pdl_wait() { asm volatile("griddepcontrol.wait;" ::: "memory"); }
+__device__ __forceinline__ void pdl_trigger() { asm volatile("griddepcontrol.launch_dependents;" ::: "memory"); }
 #endif
 
 // flag / status words other CTAs poll or publish, and single words several threads may write or read concurrently BY

@@ -65,9 +65,11 @@ __global__ void __launch_bounds__(WARPS * 32, MINB) k_canvas_fill(int32_t *__res
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     const int chunks = (plane + WCELLS - 1) / WCELLS;
     const long long wg = (long long)blockIdx.x * WARPS + warp;
-    if (wg >= (long long)chunks * batch) return;
+    pdl_trigger();
     const int b = (int)(wg / chunks);
     const int cell0 = (int)(wg % chunks) * WCELLS + lane * CPL;
+    pdl_wait();   // map, row counts and feature rows come from the kernels in front (no-op when launched plainly)
+    if (wg >= (long long)chunks * batch) return;
     long long base = (long long)b * max_voxels;
     if (MODE == 1 && compact) {   // warp-uniform: row base of frame b = voxels of the frames before it
         int s = 0;
@@ -404,7 +406,7 @@ void set_fill_variant(int v) { g_fill_variant = (v >= 0 && v <= 8) ? v : kFillDe
 template <int MODE>
 static cudaError_t run_fill(int32_t *map, const float *feats, int64_t sv, int64_t sc, const int32_t *vnum,
                             int max_voxels, int compact, int batch, int n_ch, int plane, float *canvas,
-                            cudaStream_t stream)
+                            cudaStream_t stream, bool dependent = false)
 {
     if (batch <= 0 || n_ch <= 0 || plane <= 0) return cudaSuccess;
     const bool vec_ok = (plane % 4 == 0) && ((reinterpret_cast<uintptr_t>(canvas) & 15) == 0);
@@ -448,10 +450,8 @@ static cudaError_t run_fill(int32_t *map, const float *feats, int64_t sv, int64_
         const long long warps6 = (long long)((plane + 511) / 512) * batch;
         const unsigned blocks6 = (unsigned)((warps6 + 3) / 4);
         if (feat4)
-            k_canvas_fill<MODE, true, 16, 4, 2304><<<blocks6, 128, 0, stream>>>(map, feats, sv, sc, vnum, max_voxels, compact, batch, n_ch, plane, canvas);
-        else
-            k_canvas_fill<MODE, false, 16, 4, 2304><<<blocks6, 128, 0, stream>>>(map, feats, sv, sc, vnum, max_voxels, compact, batch, n_ch, plane, canvas);
-        return cudaGetLastError();
+            return launch_k(k_canvas_fill<MODE, true, 16, 4, 2304>, dim3(blocks6), dim3(128), 0, stream, dependent, map, feats, sv, sc, vnum, max_voxels, compact, batch, n_ch, plane, canvas);
+        return launch_k(k_canvas_fill<MODE, false, 16, 4, 2304>, dim3(blocks6), dim3(128), 0, stream, dependent, map, feats, sv, sc, vnum, max_voxels, compact, batch, n_ch, plane, canvas);
     }
     if ((variant == 7 || variant == 8) && (plane % 8 != 0 || !al32)) variant = 0;
     if (variant == 7 || variant == 8) {   // experiments on the 256-cell warp: 7 = 4 warps per CTA, 8 = registers capped for 5 CTAs per SM
@@ -471,14 +471,15 @@ static cudaError_t run_fill(int32_t *map, const float *feats, int64_t sv, int64_
     const int wcells = wide ? 256 : 128;
     const long long warps = (long long)((plane + wcells - 1) / wcells) * batch;
     const unsigned blocks = (unsigned)((warps + kFillWarps - 1) / kFillWarps);
-#define PF_FILL_LAUNCH(F4, CPL) k_canvas_fill<MODE, F4, CPL><<<blocks, kFillWarps * 32, 0, stream>>>(map, feats, sv, sc, vnum, max_voxels, compact, batch, n_ch, plane, canvas)
+#define PF_FILL_LAUNCH(F4, CPL) launch_k(k_canvas_fill<MODE, F4, CPL>, dim3(blocks), dim3(kFillWarps * 32), 0, stream, dependent, map, feats, sv, sc, vnum, max_voxels, compact, batch, n_ch, plane, canvas)
+    cudaError_t le;
     if (wide) {
-        if (feat4) PF_FILL_LAUNCH(true, 8); else PF_FILL_LAUNCH(false, 8);
+        le = feat4 ? PF_FILL_LAUNCH(true, 8) : PF_FILL_LAUNCH(false, 8);
     } else {
-        if (feat4) PF_FILL_LAUNCH(true, 4); else PF_FILL_LAUNCH(false, 4);
+        le = feat4 ? PF_FILL_LAUNCH(true, 4) : PF_FILL_LAUNCH(false, 4);
     }
 #undef PF_FILL_LAUNCH
-    return cudaGetLastError();
+    return le;
 }
 
 cudaError_t launch_scatter(const Params &p, const Work &w, const float *feats, int64_t sv, int64_t sc,
@@ -498,7 +499,10 @@ cudaError_t launch_scatter_from_map(const Params &p, const Work &w, const float 
                                     int n_frames, int compact, int n_ch, float *canvas, cudaStream_t stream)
 {
     mark(w, kEvFillStart, stream);
-    const cudaError_t e = run_fill<1>(w.grid, feats, sv, sc, w.vnum, p.max_voxels, compact, n_frames, n_ch, p.plane, canvas, stream);
+    // as a programmatic dependent of whatever kernel is in front of it on the stream (the gather, or the caller's feature
+    // net): launch and index arithmetic overlap that kernel's tail, the kernel waits before it reads anything
+    const cudaError_t e = run_fill<1>(w.grid, feats, sv, sc, w.vnum, p.max_voxels, compact, n_frames, n_ch, p.plane, canvas, stream,
+                                      pdl_stage(6) && !w.ev);
     mark(w, kEvFill, stream);
     return e;
 }

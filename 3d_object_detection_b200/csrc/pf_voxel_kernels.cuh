@@ -42,6 +42,8 @@ __global__ void __launch_bounds__(256) k_quantize(Params p, Work w, const float 
                                                   int lo, int hi)
 {
     const int f = blockIdx.y;
+    if (lo == 0) pdl_wait();   // first kernel of the chain: everything in front of it on the stream is complete from here on
+    pdl_trigger();             // (after the wait, so that no later chain kernel can start before the caller's inputs are visible)
     const int base = frame_offsets[f];
     const int n_all = frame_offsets[f + 1] - base;
     const int n = n_all < hi ? n_all : hi;     // this launch covers [lo, min(n, hi)); hi <= the call's max_frame_points
@@ -53,7 +55,10 @@ __global__ void __launch_bounds__(256) k_quantize(Params p, Work w, const float 
         }
         for (int t = threadIdx.x; t < p.tiles_cap; t += 256) w.tilecnt[(size_t)f * p.tiles_cap + t] = 0;
     }
-    if (i0 >= n) return;
+    if (i0 >= n) {
+        if (lo != 0) pdl_wait();   // every CTA of a dependent grid waits: the grid must not complete before its predecessor
+        return;
+    }
     int c[kQPer];
     float x[kQPer], y[kQPer], z[kQPer];
 #pragma unroll
@@ -77,8 +82,11 @@ __global__ void __launch_bounds__(256) k_quantize(Params p, Work w, const float 
         const int i = i0 + k * 256;
         c[k] = cell_of_point(x[k], y[k], z[k], p);
         if (i < n) w.cellid[(size_t)f * p.npts_cap + i] = c[k];
-        seen[k] = c[k] >= 0 ? __ldcg(grid + c[k]) : -1;   // races with other points' atomicMin by design (see above)
     }
+    if (lo != 0) pdl_wait();   // second range: loads and quantisation above ran under the first range's tail; the probes need its grid
+#pragma unroll
+    for (int k = 0; k < kQPer; ++k)
+        seen[k] = c[k] >= 0 ? __ldcg(grid + c[k]) : -1;   // races with other points' atomicMin by design (see above)
 #pragma unroll
     for (int k = 0; k < kQPer; ++k) {
         const int i = i0 + k * 256;
@@ -108,8 +116,10 @@ __global__ void __launch_bounds__(256) k_assign(Params p, Work w, const int32_t 
     __shared__ int s_base, s_tile;
     const int f = blockIdx.y;
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    pdl_trigger();
     int n = frame_offsets[f + 1] - frame_offsets[f];
     if (n > max_frame_points) n = max_frame_points;   // an over-long frame is truncated, never half-processed
+    pdl_wait();                                       // k_quantize: tickets zeroed, grid = first index per cell
     if (tid == 0) s_tile = atomicAdd(w.ticket + f, 1);
     __syncthreads();
     const int t = s_tile;
@@ -224,15 +234,21 @@ __global__ void __launch_bounds__(kTileWarps * 32) k_tile_rank(Params p, Work w,
 {
     PF_DYN_SHARED(uint8_t, s_tbl);   // [vcols] points seen so far per voxel, this tile
     const int f = blockIdx.y, t = blockIdx.x;
+    pdl_trigger();
     int n = frame_offsets[f + 1] - frame_offsets[f];
     if (n > max_frame_points) n = max_frame_points;
     const int start = t * kTile;
-    if (start >= n) return;
+    if (start >= n) {
+        pdl_wait();   // (every CTA of a dependent grid waits, see k_quantize)
+        return;
+    }
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    // the whole table is cleared (not just the n_vox columns in use) so that this can run before k_assign has finished
+    for (int j = tid * 16; j < p.vcols; j += kTileWarps * 32 * 16) *reinterpret_cast<uint4 *>(s_tbl + j) = make_uint4(0, 0, 0, 0);
+    pdl_wait();
     const int n_vox = w.vnum[f];
     const int istar = w.istar[f];
     const int vbytes = (n_vox + 15) & ~15;
-    for (int j = tid * 16; j < vbytes; j += kTileWarps * 32 * 16) *reinterpret_cast<uint4 *>(s_tbl + j) = make_uint4(0, 0, 0, 0);
 
     const int32_t *cellid = w.cellid + (size_t)f * p.npts_cap;
     const int32_t *grid = w.grid + (size_t)f * p.cells;
@@ -309,9 +325,11 @@ __global__ void __launch_bounds__(128) k_column_scan(Params p, Work w, const int
                                                      int max_frame_points)
 {
     const int f = blockIdx.y;
+    pdl_trigger();
     int n = frame_offsets[f + 1] - frame_offsets[f];
     if (n > max_frame_points) n = max_frame_points;
     const int n_tiles = (n + kTile - 1) / kTile;
+    pdl_wait();
     const int n_vox = w.vnum[f];
     const int col = (blockIdx.x * blockDim.x + threadIdx.x) * 4;
     if (col >= n_vox) return;
@@ -350,9 +368,11 @@ __global__ void __launch_bounds__(256) k_slot(Params p, Work w, const int32_t *_
                                               int max_frame_points, int reset_grid)
 {
     const int f = blockIdx.y;
+    pdl_trigger();
     int n = frame_offsets[f + 1] - frame_offsets[f];
     if (n > max_frame_points) n = max_frame_points;
     const int i0 = blockIdx.x * (256 * kQPer) + threadIdx.x;
+    pdl_wait();
     if (i0 >= n) return;
     int vr[kQPer], cnt[kQPer];
 #pragma unroll

@@ -216,6 +216,26 @@ static cudaError_t dispatch_gather(const Params &p, const Work &w, const GatherA
                 : run_gather<32, FROM_POINTS, false>(p, w, a, grid_g32, stream);
 }
 
+// Programmatic dependent launch of the chain kernels: OFF by default, PF_PDL=1 / pf_debug_set_pdl(1) turns it on.
+// Measured (profiles/r2_chain_experiments.md E5): the second quantize range and the canvas fill as dependents save 4-5 us of a
+// serial step, the five kernels between them lose 7-10 us (the early-resident dependents take issue slots and shared memory
+// from their predecessor's tail), and with two or three front ends in flight every form of it is slower (0.290 -> 0.329 ms).
+static int g_pdl = -1;
+static int g_pdl_mask = 0x7f;   // experiments: which launches are dependents (bit 0 quantize range 2, 1 assign, 2 tile_rank,
+                                // 3 column_scan, 4 slot, 5 gather, 6 canvas fill); PF_PDL_MASK
+bool pdl_enabled()
+{
+    if (g_pdl < 0) {
+        const char *e = getenv("PF_PDL");
+        g_pdl = (e && e[0] == '1') ? 1 : 0;
+        const char *m = getenv("PF_PDL_MASK");
+        if (m) g_pdl_mask = (int)strtol(m, nullptr, 0);
+    }
+    return g_pdl != 0;
+}
+bool pdl_stage(int bit) { return pdl_enabled() && ((g_pdl_mask >> bit) & 1); }
+void set_pdl(int on) { g_pdl = on ? 1 : 0; }
+
 cudaError_t launch_voxelize(const Params &p, const Work &w, const VoxelizeArgs &a, cudaStream_t stream)
 {
     const int B = a.n_frames;
@@ -229,26 +249,36 @@ cudaError_t launch_voxelize(const Params &p, const Work &w, const VoxelizeArgs &
     // leading 1/16 of every frame first (see k_quantize); small frames go in one launch
     static const int split_den = [] { const char *e = getenv("PF_QUANTIZE_SPLIT"); const int d = e ? atoi(e) : 16; return d < 0 ? 16 : d; }();   // experiments: 0 = one launch
     const int split = (split_den > 1 && npts >= 32 * kPtsPerCta) ? ((npts / split_den + kPtsPerCta - 1) / kPtsPerCta) * kPtsPerCta : npts;
+    // Every kernel after the first is launched as a programmatic dependent of the one in front of it (pf_internal.cuh):
+    // its launch, index arithmetic and shared-memory clears run under the predecessor's tail.  Off while the stage events
+    // are recorded (an event between two kernels is a full dependency anyway).
+    const bool dep = pdl_enabled() && !w.ev;
+    cudaError_t le = cudaSuccess;
     mark(w, kEvStart, stream);
     for (int pass = 0; pass < 2; ++pass) {
         const int lo = pass == 0 ? 0 : split, hi = pass == 0 ? split : npts;
         if (lo >= hi) continue;
         const dim3 g((hi - lo + kPtsPerCta - 1) / kPtsPerCta, B);
-        if (vec4) k_quantize<true><<<g, 256, 0, stream>>>(p, w, a.points, a.frame_offsets, a.point_stride, lo, hi);
-        else      k_quantize<false><<<g, 256, 0, stream>>>(p, w, a.points, a.frame_offsets, a.point_stride, lo, hi);
+        if (vec4) le = launch_k(k_quantize<true>, g, dim3(256), 0, stream, dep && pass == 1 && pdl_stage(0), p, w, a.points, a.frame_offsets, a.point_stride, lo, hi);
+        else      le = launch_k(k_quantize<false>, g, dim3(256), 0, stream, dep && pass == 1 && pdl_stage(0), p, w, a.points, a.frame_offsets, a.point_stride, lo, hi);
+        if (le != cudaSuccess) return le;
     }
     mark(w, kEvQuantize, stream);
-    k_assign<<<dim3((npts + kATile - 1) / kATile, B), 256, 0, stream>>>(p, w, a.frame_offsets, a.voxel_num, npts);
+    le = launch_k(k_assign, dim3((npts + kATile - 1) / kATile, B), dim3(256), 0, stream, dep && pdl_stage(1), p, w, a.frame_offsets, a.voxel_num, npts);
+    if (le != cudaSuccess) return le;
     mark(w, kEvAssign, stream);
     if ((size_t)p.vcols > 48 * 1024) {
         cudaError_t e = cudaFuncSetAttribute(k_tile_rank, cudaFuncAttributeMaxDynamicSharedMemorySize, p.vcols);
         if (e != cudaSuccess) return e;
     }
-    k_tile_rank<<<g_tiles, kTileWarps * 32, p.vcols, stream>>>(p, w, a.frame_offsets, npts);
+    le = launch_k(k_tile_rank, g_tiles, dim3(kTileWarps * 32), (size_t)p.vcols, stream, dep && pdl_stage(2), p, w, a.frame_offsets, npts);
+    if (le != cudaSuccess) return le;
     mark(w, kEvTileRank, stream);
-    k_column_scan<<<dim3((p.vcols / 4 + 127) / 128, B), 128, 0, stream>>>(p, w, a.frame_offsets, npts);
+    le = launch_k(k_column_scan, dim3((p.vcols / 4 + 127) / 128, B), dim3(128), 0, stream, dep && pdl_stage(3), p, w, a.frame_offsets, npts);
+    if (le != cudaSuccess) return le;
     mark(w, kEvColumnScan, stream);
-    k_slot<<<g_pts, 256, 0, stream>>>(p, w, a.frame_offsets, npts, a.keep_cell_map ? 0 : 1);
+    le = launch_k(k_slot, g_pts, dim3(256), 0, stream, dep && pdl_stage(4), p, w, a.frame_offsets, npts, a.keep_cell_map ? 0 : 1);
+    if (le != cudaSuccess) return le;
     mark(w, kEvSlot, stream);
 
     GatherArgs ga{};

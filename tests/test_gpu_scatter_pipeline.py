@@ -435,3 +435,52 @@ def test_overlong_frame_is_truncated_on_the_device(pf):
             util.assert_vox_equal((_np(gv), _np(gc)[:, :3], _np(gn)), (v, c, n), f"bound {bound} frame {f}")
             assert np.array_equal(_np(canvas[f]), oracle.scatter(_np(pillar[f * 5000: f * 5000 + len(n)]), c, fe.nx, fe.ny)[0])
     fe.close()
+
+
+def test_pdl_switch_is_bit_identical(pf):
+    """Programmatic dependent launch of the chain (pf_debug_set_pdl, off by default): same outputs eager and in a captured
+    graph, frames of different lengths so that whole CTAs of the dependent grids have nothing to do."""
+    import importlib
+    L = importlib.import_module("3d_object_detection_b200._lib").load()
+    cfg = cfgmod.builtin_config("20cm")
+    cfg["max_voxels"] = 3000
+    geom = cfgmod.derive_grid(cfg)
+    frames = [synth.make_frame(k, geom, n, 170 + i, 9)[:n] for i, (k, n) in enumerate([("S1", 40000), ("S3", 700), ("S2", 21000)])]
+    frames.append(np.zeros((0, 4), np.float32))                      # an empty frame: every CTA of it exits at once
+    pts = torch.from_numpy(np.concatenate(frames)).cuda()
+    offs = torch.tensor(np.concatenate([[0], np.cumsum([len(f) for f in frames])]).astype(np.int32)).cuda()
+    pillar = torch.randn((4 * 3000, 64), device="cuda")
+    got = {}
+    try:
+        for on in (0, 1):
+            assert L.pf_debug_set_pdl(on) == on
+            fe = pf.PillarFrontEnd(cfg, max_batch=4, max_points_per_frame=40000, device=0)
+            canvas = fe.step(pts, offs, pillar_feats=pillar)
+            eager = [t.clone() for t in (fe.voxels, fe.coors, fe.num_points, fe.voxel_num, fe.features, canvas)]
+            fe.capture(pts, offs, pillar)
+            for t in (fe.voxels, fe.features, fe.canvas):
+                t.fill_(7.0)
+            canvas = fe.replay()
+            graph = [t.clone() for t in (fe.voxels, fe.coors, fe.num_points, fe.voxel_num, fe.features, canvas)]
+            counts = _np(fe.voxel_num)
+            mv = cfg["max_voxels"]
+            for a, b in zip(eager, graph):
+                if a.shape[0] == 4 * mv:         # slab layout: only the first voxel_num[f] rows of a frame are defined
+                    for f in range(4):
+                        sl = slice(f * mv, f * mv + int(counts[f]))
+                        assert torch.equal(a[sl].view(torch.int32), b[sl].view(torch.int32))
+                else:
+                    assert torch.equal(a.view(torch.int32), b.view(torch.int32))
+            got[on] = (graph, counts)
+            fe.close()
+    finally:
+        L.pf_debug_set_pdl(0)
+    assert got[0][1].tolist() == got[1][1].tolist() and got[0][1][3] == 0
+    mv = cfg["max_voxels"]
+    for a, b in zip(got[0][0], got[1][0]):
+        if a.shape[0] == 4 * mv:
+            for f in range(4):
+                sl = slice(f * mv, f * mv + int(got[0][1][f]))
+                assert torch.equal(a[sl].view(torch.int32), b[sl].view(torch.int32))
+        else:
+            assert torch.equal(a.view(torch.int32), b.view(torch.int32))
