@@ -12,7 +12,7 @@ LIB_PATH = Path(__file__).resolve().parent / "lib" / "libpillarfront.so"
 EXPORTS = ["pf_version", "pf_last_error_string", "pf_create", "pf_destroy", "pf_workspace_bytes",
            "pf_voxelize", "pf_voxelize_decorate", "pf_voxelize_pfn", "pf_pfn", "pf_decorate", "pf_scatter", "pf_scatter_static", "pf_scatter_from_map",
            "pf_scatter_backward", "pf_anchor_mask", "pf_nms", "pf_nms_scratch_bytes",
-           "pf_debug_stage_timing", "pf_debug_stage_times", "pf_debug_set_fill_variant", "pf_debug_set_pdl", "pf_discard_cell_map", "pf_stage_copy", "pf_copy3", "pf_upload_frames", "pf_runner_create", "pf_runner_set_slot", "pf_runner_submit",
+           "pf_debug_stage_timing", "pf_debug_stage_times", "pf_debug_set_fill_variant", "pf_debug_set_pdl", "pf_discard_cell_map", "pf_stage_copy", "pf_copy3", "pf_frame_run", "pf_frame_copy_out", "pf_upload_frames", "pf_runner_create", "pf_runner_set_slot", "pf_runner_submit",
            "pf_runner_wait", "pf_runner_destroy", "pf_runner_last_error",
            "pf_postprocess", "pf_post_scratch_bytes", "pf_post_scratch_layout"]
 
@@ -101,6 +101,10 @@ def load():
     L.pf_debug_stage_times.argtypes = [_p, C.POINTER(C.c_float), C.c_int]
     L.pf_stage_copy.restype = C.c_int
     L.pf_stage_copy.argtypes = [_p, _p, C.c_size_t, C.c_int]
+    L.pf_frame_run.restype = C.c_int
+    L.pf_frame_run.argtypes = [C.c_int, _p, _p, _p, _p, _p, _p, C.c_size_t, C.c_int, _p, C.c_int, _p, C.POINTER(C.c_int32)]
+    L.pf_frame_copy_out.restype = C.c_int
+    L.pf_frame_copy_out.argtypes = [C.c_int, _p, _p, C.c_size_t, _p, _p, C.c_size_t, _p, _p, C.c_size_t, _p, _p, C.c_int]
     L.pf_upload_frames.restype = C.c_int
     L.pf_upload_frames.argtypes = [_p, _p, C.POINTER(_p), C.POINTER(C.c_int64), C.POINTER(C.c_int32), C.c_int, C.c_int, C.c_int,
                                    C.c_int, _p, _p]

@@ -2,11 +2,15 @@
 // Declarations and the reference functions each entry point replaces: include/pillarfront.h.
 #include <cstdarg>
 #include <cstdio>
+#include <cstdlib>
 #include <cstring>
 #include <new>
 #include <string>
 
 #include <omp.h>
+#if defined(__x86_64__)
+#include <emmintrin.h>   // SSE2 (baseline x86-64): non-temporal stores for the staging copy
+#endif
 
 #include <nvtx3/nvToolsExt.h>   // header-only; a no-op unless a profiler (nsys / ncu) is attached
 
@@ -206,6 +210,48 @@ int pf_debug_stage_timing(pf_handle *h, int enable)
     return PF_OK;
 }
 
+namespace {
+
+// memcpy into a PINNED staging buffer with non-temporal stores.  A plain memcpy leaves the destination lines dirty in the
+// caches of the cores that wrote them, and the H2D DMA that follows has to pull every line out of those caches: on the
+// pool's hosts the frame graph (H2D of 1.9 MB + kernels) then takes 170-180 us on the device instead of 95
+// (profiles/r2_frame_probe.txt).  Streaming stores send the lines straight to memory and skip the read-for-ownership.
+// PF_STAGE_NT=0 selects the plain memcpy (A/B measurements).
+bool stage_streaming()
+{
+    static const bool on = [] { const char *e = getenv("PF_STAGE_NT"); return !(e && e[0] == '0'); }();
+    return on;
+}
+
+void copy_to_pinned(char *dst, const char *src, size_t bytes)
+{
+#if defined(__x86_64__)
+    if (stage_streaming() && bytes >= 4096) {
+        size_t head = (16 - (reinterpret_cast<uintptr_t>(dst) & 15)) & 15;
+        memcpy(dst, src, head);
+        dst += head, src += head, bytes -= head;
+        const size_t blocks = bytes / 64;
+        for (size_t i = 0; i < blocks; ++i) {
+            const __m128i a = _mm_loadu_si128(reinterpret_cast<const __m128i *>(src));
+            const __m128i b = _mm_loadu_si128(reinterpret_cast<const __m128i *>(src + 16));
+            const __m128i c = _mm_loadu_si128(reinterpret_cast<const __m128i *>(src + 32));
+            const __m128i d = _mm_loadu_si128(reinterpret_cast<const __m128i *>(src + 48));
+            _mm_stream_si128(reinterpret_cast<__m128i *>(dst), a);
+            _mm_stream_si128(reinterpret_cast<__m128i *>(dst + 16), b);
+            _mm_stream_si128(reinterpret_cast<__m128i *>(dst + 32), c);
+            _mm_stream_si128(reinterpret_cast<__m128i *>(dst + 48), d);
+            src += 64, dst += 64;
+        }
+        memcpy(dst, src, bytes - blocks * 64);
+        _mm_sfence();   // the stores must be globally visible before the copy engine is told to read them
+        return;
+    }
+#endif
+    memcpy(dst, src, bytes);
+}
+
+}  // namespace
+
 int pf_stage_copy(void *dst, const void *src, size_t bytes, int threads)
 {
     if (bytes == 0) return PF_OK;
@@ -214,7 +260,7 @@ int pf_stage_copy(void *dst, const void *src, size_t bytes, int threads)
     if (threads > 16) threads = 16;
     const size_t kMin = 256 * 1024;   // below this a second thread costs more than it saves
     if (threads == 1 || bytes < 2 * kMin) {
-        memcpy(dst, src, bytes);
+        copy_to_pinned(static_cast<char *>(dst), static_cast<const char *>(src), bytes);
         return PF_OK;
     }
     const size_t want = (bytes + kMin - 1) / kMin;
@@ -223,7 +269,7 @@ int pf_stage_copy(void *dst, const void *src, size_t bytes, int threads)
 #pragma omp parallel for num_threads(threads) schedule(static, 1)
     for (int t = 0; t < threads; ++t) {
         const size_t lo = (size_t)t * chunk;
-        if (lo < bytes) memcpy(static_cast<char *>(dst) + lo, static_cast<const char *>(src) + lo, bytes - lo < chunk ? bytes - lo : chunk);
+        if (lo < bytes) copy_to_pinned(static_cast<char *>(dst) + lo, static_cast<const char *>(src) + lo, bytes - lo < chunk ? bytes - lo : chunk);
     }
     return PF_OK;
 }
@@ -241,6 +287,42 @@ int pf_copy3(void *dst0, const void *src0, size_t bytes0, void *dst1, const void
         if (e != cudaSuccess) return cuda_fail(e, "pf_copy3");
     }
     return PF_OK;
+}
+
+// Host side of one VoxelGenerator.generate call in ONE library call (the interpreter costs more than the copies here):
+// stage the frame, replay the frame graph, wait, read the voxel count.
+int pf_frame_run(int device, void *graph_exec, void *stream, void *done_event, void *pending_event, void *pinned_points,
+                 const void *points, size_t bytes, int threads, int32_t *pinned_offsets, int n_points,
+                 const int32_t *pinned_voxel_num, int32_t *voxel_num)
+{
+    if (!graph_exec || !done_event || !pinned_offsets || !pinned_voxel_num || !voxel_num || n_points < 0)
+        return fail(PF_ERR_INVALID_ARGUMENT, "pf_frame_run: bad argument");
+    if (bytes > 0) {
+        if (int rc = pf_stage_copy(pinned_points, points, bytes, threads)) return rc;
+    }
+    pinned_offsets[0] = 0, pinned_offsets[1] = n_points;
+    DeviceGuard guard(device);
+    Range nvtx_range("pf_frame_run");
+    cudaStream_t st = static_cast<cudaStream_t>(stream);
+    cudaError_t e = cudaSuccess;
+    if (pending_event) e = cudaStreamWaitEvent(st, static_cast<cudaEvent_t>(pending_event), 0);
+    if (e == cudaSuccess) e = cudaGraphLaunch(static_cast<cudaGraphExec_t>(graph_exec), st);
+    if (e == cudaSuccess) e = cudaEventRecord(static_cast<cudaEvent_t>(done_event), st);
+    if (e == cudaSuccess) e = cudaEventSynchronize(static_cast<cudaEvent_t>(done_event));
+    if (e != cudaSuccess) return cuda_fail(e, "pf_frame_run");
+    *voxel_num = pinned_voxel_num[0];
+    return PF_OK;
+}
+
+int pf_frame_copy_out(int device, void *dst0, const void *src0, size_t bytes0, void *dst1, const void *src1, size_t bytes1,
+                      void *dst2, const void *src2, size_t bytes2, void *stream, void *record_event, int synchronize)
+{
+    DeviceGuard guard(device);
+    if (int rc = pf_copy3(dst0, src0, bytes0, dst1, src1, bytes1, dst2, src2, bytes2, stream)) return rc;
+    cudaError_t e = cudaSuccess;
+    if (record_event) e = cudaEventRecord(static_cast<cudaEvent_t>(record_event), static_cast<cudaStream_t>(stream));
+    if (e == cudaSuccess && synchronize) e = cudaStreamSynchronize(static_cast<cudaStream_t>(stream));
+    return e == cudaSuccess ? PF_OK : cuda_fail(e, "pf_frame_copy_out");
 }
 
 int pf_upload_frames(void *device_points, void *pinned_stage, const void *const *frames, const int64_t *rows,

@@ -3,6 +3,8 @@ fill -> D2H of the voxel count.  Used by ``VoxelGenerator.generate_and_scatter``
 infer`` loop of the reference: one frame at a time, framework/dataset.py:213-229, ros_node.py:57-75)."""
 from __future__ import annotations
 
+import ctypes as C
+
 import torch
 
 from . import _lib
@@ -27,7 +29,12 @@ class FusedFramePath:
             self.d_offs = torch.zeros((2,), dtype=torch.int32, device=self.dev)
             self.stream = torch.cuda.Stream(self.dev)
             self.event = torch.cuda.Event()
-        self.graphs = {}
+            self.event.record(self.stream)            # a torch event owns its cudaEvent_t from the first record on
+            self.stream.synchronize()
+        self.ev_done = self.event.cuda_event
+        self.p_stage, self.p_offs, self.p_vnum = self.h_pts.data_ptr(), self.h_offs.data_ptr(), self.h_vnum.data_ptr()
+        self.c_v = C.c_int32(0)
+        self.graphs = {}                              # staged rows -> (CUDAGraph, cudaGraphExec_t)
 
     def _body(self, rows: int):
         self.d_pts[:rows].copy_(self.h_pts[:rows], non_blocking=True)
@@ -47,21 +54,24 @@ class FusedFramePath:
                 with torch.cuda.graph(g, stream=self.stream):
                     self._body(rows)
             torch.cuda.synchronize(self.dev)
+            g = (g, g.raw_cuda_graph_exec())
             self.graphs[rows] = g
         return g
 
     def run(self, points, n: int, threads: int):
+        from .voxel_generator import _raw_stream
         src = points if points.flags.c_contiguous else points.copy()
-        if n:
-            _lib.check(self.fe.handle.lib.pf_stage_copy(self.np_pts.ctypes.data, src.ctypes.data, src.nbytes, threads),
-                       "pf_stage_copy")
-        self.np_offs[1] = n
         rows = min(self.cap, max(4096, (n + 4095) // 4096 * 4096))
-        g = self._graph(rows)
-        g.replay()                                    # on the caller's current stream: ordered behind the consumer of the
-        self.event.record(torch.cuda.current_stream(self.dev))      # previous canvas, in front of the consumer of this one
-        self.event.synchronize()
-        v = int(self.np_vnum[0])
+        _, exec_ptr = self._graph(rows)
+        # stage, replay on the caller's current stream (ordered behind the consumer of the previous canvas, in front of the
+        # consumer of this one), wait, read V: one foreign call
+        idx = self.dev.index
+        rc = self.fe.handle.lib.pf_frame_run(idx, exec_ptr, _raw_stream(idx), self.ev_done, None, self.p_stage,
+                                             src.ctypes.data if n else None, src.nbytes if n else 0, threads, self.p_offs, n,
+                                             self.p_vnum, C.byref(self.c_v))
+        if rc:
+            _lib.check(rc, "pf_frame_run")
+        v = self.c_v.value
         return self.fe.canvas, self.fe.coors[:v], v
 
     def close(self):

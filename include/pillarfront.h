@@ -29,7 +29,9 @@
  * Conventions
  *   - plain pointers and sizes only; every pointer named *device* is CUDA device memory on the handle's
  *     device; `stream` is a cudaStream_t passed as void*; all work is enqueued asynchronously on it and no
- *     call synchronises, allocates or frees (so every call can be captured into a CUDA graph).
+ *     call synchronises, allocates or frees (so every call can be captured into a CUDA graph).  Exceptions, all host-side
+ *     helpers of the single-frame / multi-GPU drop-in paths and documented where they are declared: pf_create / pf_destroy
+ *     (allocate), pf_frame_run and pf_frame_copy_out(synchronize = 1) and pf_runner_wait (wait for the device).
  *   - every function returns 0 on success, a negative pf_status on bad arguments, or a positive
  *     cudaError_t; it never throws.  pf_last_error_string() describes the last failure of the calling thread.
  *   - a handle is bound to one device and is not re-entrant: use one handle per (GPU, stream).
@@ -95,6 +97,23 @@ PF_API int pf_stage_copy(void *dst, const void *src, size_t bytes, int threads);
  * read the voxel count (one library call instead of three framework copies).  A zero size skips that copy. */
 PF_API int pf_copy3(void *dst0, const void *src0, size_t bytes0, void *dst1, const void *src1, size_t bytes1,
                     void *dst2, const void *src2, size_t bytes2, void *stream);
+
+/* Host side of ONE single-frame call (VoxelGenerator.generate, framework/voxel_generator.py:28-40; the reference's operating
+ * point is one frame per call) in one library call, so that the host language pays one foreign call instead of six:
+ * copy `bytes` of `points` (pageable) into `pinned_points` with up to `threads` host threads, write the frame offsets
+ * {0, n_points} into `pinned_offsets`, make `stream` wait for `pending_event` (may be NULL: a hand-out copy of the previous
+ * call on another stream), launch `graph_exec` -- a cudaGraphExec_t the caller captured once: H2D of the staged frame and
+ * offsets, pf_voxelize*, D2H of the voxel count into `pinned_voxel_num` -- on `stream`, record `done_event` (a cudaEvent_t
+ * of the caller), wait for it and return the voxel count.  `device` is made current for the call.  This is the only call of
+ * the library that synchronises, by design: the row count of the outputs is data dependent. */
+PF_API int pf_frame_run(int device, void *graph_exec, void *stream, void *done_event, void *pending_event,
+                        void *pinned_points, const void *points, size_t bytes, int threads, int32_t *pinned_offsets,
+                        int n_points, const int32_t *pinned_voxel_num, int32_t *voxel_num);
+/* The hand-out that follows: pf_copy3, then `record_event` (may be NULL) recorded on `stream`, then, if `synchronize`, a wait
+ * for the stream (pinned host destinations that are returned to the caller as numpy arrays). */
+PF_API int pf_frame_copy_out(int device, void *dst0, const void *src0, size_t bytes0, void *dst1, const void *src1,
+                             size_t bytes1, void *dst2, const void *src2, size_t bytes2, void *stream, void *record_event,
+                             int synchronize);
 
 /* Batched multi-frame upload (the collate + H2D of row N3, framework/utils.py:23-48, for a list of per-frame arrays): copies
  * `n_frames` frames back to back into `device_points` on `stream` and writes the frame offsets (n_slots + 1 int32, frames

@@ -384,3 +384,19 @@ def test_bench_rank_placement():
         os.environ.pop("PF_DEVICE_MAP", None)
         if old is not None:
             os.environ["PF_DEVICE_MAP"] = old
+
+
+def test_stage_copy_streaming_stores_copy_exactly():
+    """pf_stage_copy (non-temporal stores into the pinned staging buffer): every size / misalignment / thread count copies
+    exactly the requested bytes and nothing around them.  Pure host code, no GPU."""
+    L = importlib.import_module("3d_object_detection_b200._lib").load()
+    rng = np.random.default_rng(0)
+    for n in (0, 1, 15, 64, 4095, 4096, 4097, 100003, 600000, 1920001):
+        for off_s, off_d in ((0, 0), (3, 0), (0, 5), (7, 9)):
+            src = rng.integers(0, 255, n + 16, dtype=np.uint8)
+            dst = np.zeros(n + 32, np.uint8)
+            for thr in (1, 4, 16):
+                dst[:] = 0
+                assert L.pf_stage_copy(dst.ctypes.data + off_d, src.ctypes.data + off_s, n, thr) == 0
+                assert np.array_equal(dst[off_d:off_d + n], src[off_s:off_s + n]), (n, off_s, off_d, thr)
+                assert not dst[:off_d].any() and not dst[off_d + n:].any()

@@ -39,8 +39,10 @@ def t(fn, reps=200):
     return 1e6 * (time.perf_counter() - t0) / reps
 
 
-rows = vg._stage(path, frame, n)
-g = path.graph_for(rows)
+rows = min(path.cap, max(4096, (n + 4095) // 4096 * 4096))
+g, g_exec = path.graph_for(rows)
+lib.pf_stage_copy(path.np_pts.ctypes.data, frame.ctypes.data, frame.nbytes, 4)
+path.np_offs[0], path.np_offs[1] = 0, n
 print(f"{a.grid}: frame of {n} points, staged rows {rows}, host threads {vg._threads}")
 for thr in (1, 2, 4, 8):
     print(f"  pf_stage_copy {frame.nbytes / 1e6:.2f} MB, {thr} threads: {t(lambda: lib.pf_stage_copy(path.np_pts.ctypes.data, frame.ctypes.data, frame.nbytes, thr)):7.1f} us")
@@ -55,6 +57,25 @@ def replay_wait():
 
 
 print(f"  graph replay (H2D + 7 kernels + D2H of V) + event wait: {t(replay_wait):7.1f} us")
+import ctypes as C  # noqa: E402
+c_v = C.c_int32(0)
+raw = torch.cuda.current_stream(path.dev).cuda_stream
+side = path.stream.cuda_stream
+for name, st in (("current (default) stream", raw), ("side stream", side)):
+    for thr in (0, vg._threads):
+        nb = frame.nbytes if thr else 0
+        print(f"  pf_frame_run on the {name}, stage threads {thr}: "
+              f"{t(lambda: lib.pf_frame_run(path.dev.index, g_exec, st, path.ev_done, None, path.p_stage, frame.ctypes.data, nb, max(thr, 1), path.p_offs, n, path.p_vnum, C.byref(c_v))):7.1f} us")
+
+
+def replay_wait_default():
+    g.replay()
+    path.event.record(torch.cuda.current_stream(path.dev))
+    path.event.synchronize()
+
+
+print(f"  torch replay + event wait on the current (default) stream: {t(replay_wait_default):7.1f} us")
+print(f"  torch replay + event wait on the side stream again:        {t(replay_wait):7.1f} us")
 e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
 with torch.cuda.stream(path.stream):
     e0.record(path.stream)
