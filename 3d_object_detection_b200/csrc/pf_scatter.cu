@@ -14,7 +14,10 @@
 namespace pf {
 
 constexpr int kFillDefault = -1;   // auto: 32-byte stores, one warp per 256 cells, or per 512 cells on canvases of >= 2^25 cells
-                                   // (profiles/r2_fill_variants.md: 20 cm x 8 238 vs 239 us, nuScenes x 8 109 vs 118 us, 10 cm x 32 3281 vs 3176 us)
+                                   // (profiles/r2_fill_variants.md: 20 cm x 8 238 vs 239 us, nuScenes x 8 109 vs 118 us, 10 cm x 32 3281 vs 3176 us);
+                                   // 16-byte stores, one warp per 128 cells, on canvases of one or two frames, where twice the
+                                   // warps matter more than the wider store (20 cm x 1: 32.7 vs 45.3 us, 16 cm x 1: 46.9 vs 49.7 us)
+constexpr long long kFillSmallCells = 1310720;   // 1.25 * 2^20 cells: two 20 cm frames, one 16 cm frame
 
 // map[b][x*ny+y] = max(row) over pillars in that cell  (highest row wins == sequential index_put)
 __global__ void __launch_bounds__(256) k_map_index(const int32_t *__restrict__ coors, int coors_stride,
@@ -419,7 +422,10 @@ static cudaError_t run_fill(int32_t *map, const float *feats, int64_t sv, int64_
         return cudaGetLastError();
     }
     int variant = fill_variant();
-    if (variant < 0) variant = ((long long)batch * plane >= (1ll << 25)) ? 6 : 1;
+    if (variant < 0) {   // the rule behind kFillDefault
+        const long long cells = (long long)batch * plane;
+        variant = cells >= (1ll << 25) ? 6 : (cells <= kFillSmallCells ? 0 : 1);
+    }
     const bool feat4 = (sc == 1) && (sv % 4 == 0) && (n_ch % 4 == 0) && ((reinterpret_cast<uintptr_t>(feats) & 15) == 0);
     if (variant >= 2 && variant <= 5) {
         // 2: 128-cell chunks x 64 channels (512-byte copies); 3: the same + L2 evict-first; 4: 512-cell chunks x 16 channels

@@ -157,7 +157,7 @@ PF_API int pf_debug_stage_timing(pf_handle *h, int enable);
  * cells, 32-byte streaming stores (STG.256, the default); 2 = TMA bulk stores of shared-memory tiles (cp.async.bulk,
  * UBLKCP), 512 bytes per copy; 3 = as 2 with an L2 evict-first hint; 4 / 5 = as 2 / 3 with 2 KB per copy; 6 = one warp
  * per 512 cells, two 32-byte stores per lane and channel; -1 = the library default: 6 for canvases of at least 2^25 cells
- * (batch * nx * ny), else 1.  Every variant writes the same bytes.  Returns the
+ * (batch * nx * ny), 0 for canvases of at most 1.25 * 2^20 cells (one or two frames), else 1.  Every variant writes the same bytes.  Returns the
  * variant now in force, or a negative pf_status. */
 PF_API int pf_debug_set_fill_variant(int variant);
 /* Diagnostics / A-B measurements: programmatic dependent launch of the chain (process-wide; also the environment variables
