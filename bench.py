@@ -702,6 +702,16 @@ def host_link_ceiling(n_gpus):
     return None
 
 
+def fill_kernel_name(variant, cells):
+    """Which canvas-fill kernel pf_scatter_from_map launched (the rule of run_fill, csrc/pf_scatter.cu)."""
+    if variant < 0:
+        variant = 6 if cells >= 1 << 25 else (0 if cells <= 1310720 else 1)
+    names = {0: "k_canvas_fill<1,1,4> (one warp per 128 cells, 16-byte streaming stores)",
+             1: "k_canvas_fill<1,1,8> (one warp per 256 cells, 32-byte streaming stores)",
+             6: "k_canvas_fill<1,1,16,4,2304> (one warp per 512 cells, 32-byte streaming stores)"}
+    return names.get(variant, f"canvas fill variant {variant} (pf_debug_set_fill_variant)") + ", pf_scatter_from_map"
+
+
 def ncu_traffic(grid, batch):
     """DRAM bytes of one canvas-fill launch from the committed ncu capture of this workload (shipped kernel set), else None."""
     try:
@@ -760,7 +770,8 @@ def main():
         "single_frame_api": r["single"],
         "e2e_hbm_frac": r["bytes_alg"]["e2e"] / (r["t_dev"] / K) / 1e9 / peak,
         "e2e_hbm_frac_serial": r["bytes_alg"]["e2e"] / r["t_serial"] / 1e9 / peak,
-        "roofline": {"kernel": "k_canvas_fill<1,1,8> (pf_scatter_from_map, 32-byte streaming stores)", "bound": "hbm", "achieved": achieved,
+        "roofline": {"kernel": fill_kernel_name(r["fill_variant"], B * int(r["geom"].grid_size[0]) * int(r["geom"].grid_size[1])),
+                     "bound": "hbm", "achieved": achieved,
                      "peak": peak, "unit": "GB/s", "frac": achieved / peak, "traffic": ncu_traffic(args.grid, B),
                      "peak_source": peak_src, "frac_of_nominal_8TBs": achieved / 8000.0,
                      "bytes_per_launch": scat_bytes, "ms_per_launch": 1e3 * r["t_scat"],
