@@ -11,8 +11,10 @@ The single-frame path is the reference's real operating point (every ``configs/*
 * per instance and per ``(F, point-capacity bucket)`` one :class:`_FramePath` -- workspace handle, device buffers, a
   PINNED input staging buffer, and ONE CUDA graph holding "H2D of the staged frame + frame length, the voxelise
   kernels, D2H of the voxel count"; nothing is allocated, no ``torch.tensor(...)`` / ``.item()`` per call;
-* the numpy frame is copied into the staging buffer by ``pf_stage_copy`` (a few host threads), the graph is replayed,
-  the host waits on one event and reads ``V`` from pinned memory, then copies exactly ``V`` rows out;
+* ONE foreign call per frame (``pf_frame_run``): the numpy frame is copied into the staging buffer by a few host threads
+  with non-temporal stores (a plain memcpy leaves dirty cache lines the copy engine then has to pull out of the CPU caches:
+  +45 us on the H2D), the graph is replayed on the caller's current stream, the host waits on one event and reads ``V``
+  from pinned memory; a second call (``pf_frame_copy_out``) copies exactly ``V`` rows out;
 * numpy outputs land directly in a pinned block taken from a small recycling pool and are returned as views of it:
   a block is only handed out again once every array that was returned from it has been released (the reference's
   ownership contract -- callers may keep the arrays -- holds; nothing aliases a live result; an asynchronous copy a
