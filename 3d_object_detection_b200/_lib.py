@@ -203,3 +203,37 @@ class Handle:
             self.close()
         except Exception:
             pass
+
+
+# ---- cheap torch plumbing for the per-call host paths (a Stream object or a device context costs 5-8 us each) ----------
+_RAW_STREAM = None
+
+
+def raw_stream(device_index: int) -> int:
+    """cudaStream_t of torch's current stream on the device, without building a torch.cuda.Stream object."""
+    global _RAW_STREAM
+    if _RAW_STREAM is None:
+        import torch
+        fast = getattr(torch._C, "_cuda_getCurrentRawStream", None)
+        _RAW_STREAM = fast if fast is not None else (lambda idx: torch.cuda.current_stream(idx).cuda_stream)
+    return _RAW_STREAM(device_index)
+
+
+class _NoCtx:
+    def __enter__(self):
+        return self
+
+    def __exit__(self, *exc):
+        return False
+
+
+_NO_CTX = _NoCtx()
+
+
+def on_device(device):
+    """Context that makes `device` current for handle-free library calls; free when it already is."""
+    import torch
+    idx = device.index if device.index is not None else torch.cuda.current_device()
+    if torch.cuda.current_device() == idx:
+        return _NO_CTX
+    return torch.cuda.device(idx)

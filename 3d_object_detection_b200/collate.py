@@ -76,4 +76,19 @@ def example_convert_to_torch(example, dtype=None, device=None):
     device = torch.device("cuda:0") if device is None else torch.device(device)
     casts = {"voxels": torch.float32 if dtype is None else dtype, "anchors_mask": torch.bool}
     casts.update({k: torch.int32 for k in _INT32_KEYS})
-    return {k: (torch.as_tensor(v, dtype=casts[k], device=device) if k in casts else v) for k, v in example.items()}
+    out, pending = {}, False
+    for k, v in example.items():
+        if k not in casts:
+            out[k] = v
+        elif device.type == "cuda" and isinstance(v, np.ndarray) and v.flags.c_contiguous and v.flags.writeable:
+            # numpy -> CUDA: all copies are issued first and waited for ONCE (torch.as_tensor waits after each).  The arrays
+            # VoxelGenerator.generate returns are views of pinned blocks, so these are plain DMA transfers; the single wait
+            # below keeps the reference's contract that the source may be dropped as soon as this function returns.
+            t = torch.from_numpy(v).to(device, non_blocking=True)
+            out[k] = t if t.dtype == casts[k] else t.to(casts[k])
+            pending = True
+        else:
+            out[k] = torch.as_tensor(v, dtype=casts[k], device=device)
+    if pending:
+        torch.cuda.current_stream(device).synchronize()
+    return out

@@ -59,8 +59,8 @@ def decorate(voxels, num_points, coors, vx, vy, x_offset, y_offset):
         raise ValueError("num_points / coors do not match voxels")
     out = torch.empty((v, p, f + 5), dtype=torch.float32, device=voxels.device)
     lib = _lib.load()
-    with torch.cuda.device(voxels.device):
-        stream = torch.cuda.current_stream(voxels.device).cuda_stream
+    with _lib.on_device(voxels.device):
+        stream = _lib.raw_stream(voxels.device.index)
         _lib.check(lib.pf_decorate(voxels.data_ptr(), num_points.data_ptr(), coors.data_ptr(), int(coors.shape[1]),
                                    v, p, f, vx, vy, x_offset, y_offset, out.data_ptr(), stream), "pf_decorate")
     return out
@@ -94,8 +94,8 @@ def pfn_fused(voxels, num_points, coors, vx, vy, x_offset, y_offset, weight, sca
     coors = coors.to(device=voxels.device, dtype=torch.int32).contiguous()
     out = torch.empty((v, 64), dtype=torch.float32, device=voxels.device)
     lib = _lib.load()
-    with torch.cuda.device(voxels.device):
-        stream = torch.cuda.current_stream(voxels.device).cuda_stream
+    with _lib.on_device(voxels.device):
+        stream = _lib.raw_stream(voxels.device.index)
         _lib.check(lib.pf_pfn(voxels.data_ptr(), num_points.data_ptr(), coors.data_ptr(), int(coors.shape[1]), v, p, f,
                               vx, vy, x_offset, y_offset, weight.data_ptr(), scale.data_ptr(), shift.data_ptr(), 64,
                               out.data_ptr(), stream), "pf_pfn")
@@ -169,7 +169,7 @@ def _scatter_handle(nx: int, ny: int, batch: int, device: torch.device) -> "_lib
     """Workspace holding the cell->row map for a stand-alone scatter: one per (device, STREAM, plane) -- a handle is
     not re-entrant (include/pillarfront.h), and two modules running on different streams must not share one map."""
     idx = device.index if device.index is not None else torch.cuda.current_device()
-    key = (idx, torch.cuda.current_stream(idx).cuda_stream, nx, ny)
+    key = (idx, _lib.raw_stream(idx), nx, ny)
     h = _SCATTER_HANDLES.get(key)
     if h is None or h.max_frames < batch:
         if h is not None:
@@ -187,8 +187,8 @@ def _scatter_raw(feats, sv, sc, coors, n_vox, batch, n_ch, nx, ny, out=None):
     dev = feats.device
     h = _scatter_handle(nx, ny, batch, dev)
     canvas = out if out is not None else torch.empty((batch, n_ch, nx, ny), dtype=torch.float32, device=dev)
-    with torch.cuda.device(dev):
-        stream = torch.cuda.current_stream(dev).cuda_stream
+    with _lib.on_device(dev):
+        stream = _lib.raw_stream(dev.index)
         _lib.check(h.lib.pf_scatter(h.ptr, feats.data_ptr(), sv, sc, coors.data_ptr(), int(coors.shape[1]),
                                     n_vox, batch, n_ch, canvas.data_ptr(), stream), "pf_scatter")
     return canvas
@@ -211,8 +211,8 @@ class _ScatterFn(torch.autograd.Function):
         n_vox = coords.shape[0]
         out = torch.empty((n_vox, n_ch), dtype=torch.float32, device=g.device)
         lib = _lib.load()
-        with torch.cuda.device(g.device):
-            stream = torch.cuda.current_stream(g.device).cuda_stream
+        with _lib.on_device(g.device):
+            stream = _lib.raw_stream(g.device.index)
             _lib.check(lib.pf_scatter_backward(g.data_ptr(), coords.data_ptr(), int(coords.shape[1]), n_vox, batch,
                                                n_ch, nx, ny, out.data_ptr(), n_ch, 1, stream), "pf_scatter_backward")
         return out, None, None, None, None
@@ -237,6 +237,11 @@ class PointPillarsScatter(nn.Module):
         if self.batch_size > 1 and coords.shape[1] < 4:
             raise ValueError("batch_size > 1 needs coords (V, 4) with the frame id in the last column")
         coords = coords.to(device=voxel_features.device)
+        if not (torch.is_grad_enabled() and voxel_features.requires_grad):      # inference: no autograd node to build
+            feats = voxel_features.contiguous()
+            coords = coords.to(dtype=torch.int32).contiguous()
+            return _scatter_raw(feats, feats.shape[1], 1, coords, feats.shape[0], int(self.batch_size), feats.shape[1],
+                                self.nx, self.ny)
         return _ScatterFn.apply(voxel_features, coords, int(self.batch_size), self.nx, self.ny)
 
 

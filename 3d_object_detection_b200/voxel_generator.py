@@ -56,17 +56,7 @@ def _torch():
     return torch
 
 
-_RAW_STREAM = None
-
-
-def _raw_stream(device_index: int) -> int:
-    """cudaStream_t of torch's current stream on the device, without building a Stream object (8 us -> 0.3 us)."""
-    global _RAW_STREAM
-    if _RAW_STREAM is None:
-        torch = _torch()
-        fast = getattr(torch._C, "_cuda_getCurrentRawStream", None)
-        _RAW_STREAM = fast if fast is not None else (lambda idx: torch.cuda.current_stream(idx).cuda_stream)
-    return _RAW_STREAM(device_index)
+_raw_stream = _lib.raw_stream
 
 
 def _stage_threads() -> int:

@@ -502,11 +502,13 @@ def run_b200(args, rank, world, local):
         net1 = pfm.PointNet(4, cfg["voxel_size"], geom.offset).to(dev).eval()
         scat1 = pfm.PointPillarsScatter(1, geom.grid_size, 64)
         frame0 = frames[0]
+        to_torch = importlib.import_module("3d_object_detection_b200.collate").example_convert_to_torch
 
         def one_frame(device_outputs):
             v, c, n = vg.generate(frame0, device_outputs=device_outputs)       # numpy in (pageable), like dataset.py:215
-            if not device_outputs:                                             # example_convert_to_torch, utils.py:7-20
-                v, c, n = (torch.as_tensor(x, device=dev) for x in (v, c, n))
+            if not device_outputs:                      # the package's drop-in for example_convert_to_torch, utils.py:7-20
+                ex = to_torch({"voxels": v, "coordinates": c, "num_points_per_voxel": n}, device=dev)
+                v, c, n = ex["voxels"], ex["coordinates"], ex["num_points_per_voxel"]
             with torch.no_grad():
                 canvas1 = scat1(net1(v, n, c).reshape(-1, 64), c)
             torch.cuda.synchronize(dev)
