@@ -216,6 +216,9 @@ def raw_stream(device_index: int) -> int:
         import torch
         fast = getattr(torch._C, "_cuda_getCurrentRawStream", None)
         _RAW_STREAM = fast if fast is not None else (lambda idx: torch.cuda.current_stream(idx).cuda_stream)
+    if device_index is None:
+        import torch
+        device_index = torch.cuda.current_device()
     return _RAW_STREAM(device_index)
 
 

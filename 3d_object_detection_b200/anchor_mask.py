@@ -81,8 +81,8 @@ def anchor_mask_device(coors, shape, anchor_coors_cuda, anchors_mask_cuda=None, 
     if coors.dtype != torch.int32 or coors.dim() != 2 or coors.shape[1] < 2 or (coors.numel() and coors.stride(1) != 1):
         raise ValueError("coors must be a CUDA int32 (rows, >=2) tensor with unit column stride")
     row_stride = int(coors.stride(0)) if coors.shape[0] > 1 else int(coors.shape[1])
-    stream = torch.cuda.current_stream(dev).cuda_stream
-    with torch.cuda.device(dev):
+    stream = _lib.raw_stream(dev.index)
+    with _lib.on_device(dev):
         _lib.check(lib.pf_anchor_mask(coors.data_ptr() if coors.numel() else None, row_stride,
                                       voxel_num.data_ptr() if voxel_num is not None else None, int(coors.shape[0]),
                                       int(rows_per_frame), int(n_frames), nx, ny, anchor_coors_cuda.data_ptr(), A,

@@ -75,7 +75,7 @@ class PillarFrontEnd:
         mfp = self.max_points_per_frame if max_frame_points is None else int(max_frame_points)
         h = self.handle
         vx, vy, xo, yo = self.consts
-        stream = torch.cuda.current_stream(self.device).cuda_stream
+        stream = _lib.raw_stream(self.device.index)
         _lib.check(h.lib.pf_voxelize_decorate(
             h.ptr, points.data_ptr(), frame_offsets.data_ptr(), n_frames, mfp, int(points.shape[1]),
             1 if self.compact else 0, 4, vx, vy, xo, yo, 1 if keep_cell_map else 0,
@@ -86,7 +86,7 @@ class PillarFrontEnd:
     def discard_cell_map(self):
         """Drop the cell map a voxelise call kept when no scatter follows it."""
         h = self.handle
-        _lib.check(h.lib.pf_discard_cell_map(h.ptr, torch.cuda.current_stream(self.device).cuda_stream), "pf_discard_cell_map")
+        _lib.check(h.lib.pf_discard_cell_map(h.ptr, _lib.raw_stream(self.device.index)), "pf_discard_cell_map")
 
     def voxelize_pfn(self, points, frame_offsets, folded, n_frames=None, max_frame_points=None, want_features=False):
         """Fused voxelise + decorate + PFN (pf_voxelize_pfn): fills voxels/coors/num/voxel_num and ``self.pillar_feats``
@@ -98,7 +98,7 @@ class PillarFrontEnd:
         w, sc, sh = folded
         h = self.handle
         vx, vy, xo, yo = self.consts
-        stream = torch.cuda.current_stream(self.device).cuda_stream
+        stream = _lib.raw_stream(self.device.index)
         _lib.check(h.lib.pf_voxelize_pfn(
             h.ptr, points.data_ptr(), frame_offsets.data_ptr(), n_frames, mfp, int(points.shape[1]),
             1 if self.compact else 0, 4, vx, vy, xo, yo, 1, w.data_ptr(), sc.data_ptr(), sh.data_ptr(), 64,
@@ -112,7 +112,7 @@ class PillarFrontEnd:
         """pillar_feats: CUDA fp32 (rows, C) row-major, rows laid out like the voxel outputs."""
         n_frames = self.B if n_frames is None else int(n_frames)
         h = self.handle
-        stream = torch.cuda.current_stream(self.device).cuda_stream
+        stream = _lib.raw_stream(self.device.index)
         _lib.check(h.lib.pf_scatter_from_map(h.ptr, pillar_feats.data_ptr(), int(pillar_feats.stride(0)),
                                              int(pillar_feats.stride(1)), n_frames, 1 if self.compact else 0,
                                              self.C, self.canvas.data_ptr(), stream), "pf_scatter_from_map")

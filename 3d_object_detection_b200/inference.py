@@ -96,12 +96,12 @@ class PostProcessor:
                 raise ValueError(f"anchors_mask must be a CUDA bool / uint8 tensor of shape {(B, A)}")
             anchors_mask = anchors_mask.contiguous()
             mask_ptr = anchors_mask.data_ptr()
-        with torch.cuda.device(self.device):
+        with _lib.on_device(self.device):
             _lib.check(self.lib.pf_postprocess(
                 C.byref(self.desc), cls_preds.data_ptr(), box_preds.data_ptr(), dir_preds.data_ptr(), mask_ptr,
                 self.anchors.data_ptr(), B, A, self.scratch.data_ptr(), self.det_boxes.data_ptr(),
                 self.det_scores.data_ptr(), self.det_class.data_ptr(), self.det_anchor.data_ptr(), self.det_num.data_ptr(),
-                torch.cuda.current_stream(self.device).cuda_stream), "pf_postprocess")
+                _lib.raw_stream(self.device.index)), "pf_postprocess")
         return self.det_boxes[:B], self.det_scores[:B], self.det_class[:B], self.det_anchor[:B], self.det_num[:B]
 
     def region(self, name, n_frames):

@@ -37,7 +37,7 @@ def _scratch_for(dev, n_seg, max_seg):
     need = int(lib.pf_nms_scratch_bytes(int(n_seg), int(max_seg)))
     if need == 0:
         raise ValueError(f"unsupported NMS size: {n_seg} segments of up to {max_seg} boxes (limit {MAX_SEGMENT_BOXES})")
-    key = (dev.index, torch.cuda.current_stream(dev).cuda_stream)
+    key = (dev.index, _lib.raw_stream(dev.index))
     buf = _scratch.get(key)
     if buf is None or buf.numel() < need:
         buf = torch.empty((need,), dtype=torch.uint8, device=dev)
@@ -72,12 +72,12 @@ def nms_device(boxes, scores, seg_offsets=None, max_segment_boxes=None, iou_thre
         keep = torch.empty((n_seg, post), dtype=torch.int32, device=dev)
     if keep_num is None:
         keep_num = torch.empty((n_seg,), dtype=torch.int32, device=dev)
-    with torch.cuda.device(dev):
+    with _lib.on_device(dev):
         scratch = _scratch_for(dev, n_seg, max_segment_boxes)
         _lib.check(lib.pf_nms(boxes.data_ptr() if n_total else None, scores.data_ptr() if n_total else None,
                               seg_offsets.data_ptr() if seg_offsets is not None else None, n_seg, n_total,
                               int(max_segment_boxes), float(iou_threshold), post, scratch.data_ptr(), keep.data_ptr(),
-                              keep_num.data_ptr(), torch.cuda.current_stream(dev).cuda_stream), "pf_nms")
+                              keep_num.data_ptr(), _lib.raw_stream(dev.index)), "pf_nms")
     return keep, keep_num
 
 
