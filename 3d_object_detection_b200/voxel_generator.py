@@ -185,6 +185,7 @@ class VoxelGenerator:
         self._fused = {}        # (F, capacity, id(pfn)) -> _FusedPath (generate_and_scatter)
         self._threads = _stage_threads()
         self._cuda_ok = False
+        self._batch_stage = None   # pinned staging of generate_batch for lists of numpy frames
         import threading
         self._lock = threading.Lock()   # the reference's generate is a pure function and therefore thread-safe; this one owns
                                         # buffers, so concurrent calls on ONE instance are serialised (use one instance per thread
@@ -340,13 +341,53 @@ class VoxelGenerator:
         if not 3 <= n_feat <= 16:
             raise ValueError(f"point features must be 3..16, got {n_feat}")
         sizes = [int(f.shape[0]) for f in frames_dev]
-        max_pts = max(sizes + [1])
-        h = self._handle(n_frames, n_feat, max_pts)
         with torch.cuda.device(dev):
             pts = frames_dev[0] if n_frames == 1 else torch.cat(frames_dev, dim=0)
             if pts.numel() == 0:
                 pts = torch.zeros((1, n_feat), dtype=torch.float32, device=dev)
             offs = torch.tensor(np.concatenate([[0], np.cumsum(sizes)]).astype(np.int32), device=dev)
+        return self._voxelize_batch(pts, offs, n_frames, n_feat, max(sizes + [1]), compact, coors_stride)
+
+    def _run_host(self, frames, n_feat: int, compact: bool, coors_stride: int):
+        """A list of C-contiguous float32 numpy frames: ONE pf_upload_frames call stages them (streaming stores, a few host
+        threads) into a pinned buffer and enqueues one DMA per frame, instead of a pageable copy + wait per frame."""
+        torch = _torch()
+        dev = torch.device("cuda", self._device_index)
+        n_frames = len(frames)
+        sizes = [int(f.shape[0]) for f in frames]
+        total = max(1, sum(sizes))
+        st = self._batch_stage
+        if st is None or st["F"] != n_feat or st["rows"] < total or st["frames"] < n_frames:
+            rows = max(total, st["rows"] if st and st["F"] == n_feat else 0)
+            rows = (rows + _BUCKET - 1) // _BUCKET * _BUCKET
+            slots = max(n_frames, st["frames"] if st else 0)
+            torch.cuda.synchronize(dev)                       # the DMA of an earlier batch may still read the old buffer
+            with torch.cuda.device(dev):
+                st = dict(F=n_feat, rows=rows, frames=slots, h_pts=torch.empty((rows, n_feat), dtype=torch.float32).pin_memory(),
+                          h_offs=torch.zeros((slots + 1,), dtype=torch.int32).pin_memory(), event=torch.cuda.Event())
+            st["ptrs"], st["nrows"], st["kinds"] = (C.c_void_p * slots)(), (C.c_int64 * slots)(), (C.c_int32 * slots)()
+            st["busy"] = False
+            self._batch_stage = st
+        if st["busy"]:
+            st["event"].synchronize()                         # the previous batch's DMA out of the staging buffer
+        for b, f in enumerate(frames):
+            st["ptrs"][b], st["nrows"][b], st["kinds"][b] = f.ctypes.data if sizes[b] else None, sizes[b], 0
+        with torch.cuda.device(dev):
+            pts = torch.empty((total, n_feat), dtype=torch.float32, device=dev)
+            raw = _raw_stream(self._device_index)
+            lib = _lib.load()
+            _lib.check(lib.pf_upload_frames(pts.data_ptr(), st["h_pts"].data_ptr(), st["ptrs"], st["nrows"], st["kinds"], n_frames,
+                                            n_frames, n_feat * 4, self._threads, st["h_offs"].data_ptr(), raw), "pf_upload_frames")
+            offs = st["h_offs"][:n_frames + 1].to(dev, non_blocking=True)
+            st["event"].record(torch.cuda.current_stream(dev))
+            st["busy"] = True
+        return self._voxelize_batch(pts, offs, n_frames, n_feat, max(sizes + [1]), compact, coors_stride)
+
+    def _voxelize_batch(self, pts, offs, n_frames: int, n_feat: int, max_pts: int, compact: bool, coors_stride: int):
+        torch = _torch()
+        dev = torch.device("cuda", self._device_index)
+        h = self._handle(n_frames, n_feat, max_pts)
+        with torch.cuda.device(dev):
             rows = n_frames * self.max_voxels
             voxels = torch.empty((rows, self.max_num_points, n_feat), dtype=torch.float32, device=dev)
             coors = torch.empty((rows, coors_stride), dtype=torch.int32, device=dev)
@@ -387,9 +428,16 @@ class VoxelGenerator:
         """List of frames -> dict in the collated layout of merge_second_batch (framework/utils.py:23-48)."""
         if len(frames) == 0:
             raise ValueError("generate_batch needs at least one frame")
-        devs = [self._to_device(f)[0] for f in frames]
         stride = 4 if len(frames) > 1 else 3       # merge_second_batch pads the frame id only when B > 1
-        voxels, coors, num, vnum = self._run(devs, compact=True, coors_stride=stride)
+        kinds = [self._check_points(f) for f in frames]
+        if all(k[0] == "numpy" for k in kinds) and len({k[2] for k in kinds}) == 1:
+            self._require_cuda()
+            host = [f if f.flags.c_contiguous else np.ascontiguousarray(f) for f in frames]
+            with self._lock:
+                voxels, coors, num, vnum = self._run_host(host, kinds[0][2], compact=True, coors_stride=stride)
+        else:
+            devs = [self._to_device(f)[0] for f in frames]
+            voxels, coors, num, vnum = self._run(devs, compact=True, coors_stride=stride)
         counts = vnum.cpu().numpy()
         total = int(counts.sum())
         out = {"voxels": voxels[:total], "coordinates": coors[:total], "num_points_per_voxel": num[:total],

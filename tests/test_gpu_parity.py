@@ -135,6 +135,18 @@ def test_voxelize_batch_collated(pfm):
     want_c = np.concatenate([np.pad(r[1], ((0, 0), (0, 1)), constant_values=i) for i, r in enumerate(refs)])
     want_n = np.concatenate([r[2] for r in refs])
     util.assert_vox_equal((out["voxels"], out["coordinates"], out["num_points_per_voxel"]), (want_v, want_c, want_n))
+    # the staged host-frame path again: a bigger batch (staging grows), a smaller one right after (staging reused while the
+    # previous DMA may still be in flight), a Fortran-ordered frame, and a mixed list (CUDA tensor inside -> device path)
+    import torch
+    big = [synth.make_frame("S2", geom, 40000, 400 + i, 700) for i in range(3)]
+    for batch in (big, frames[:2], [np.asfortranarray(frames[0]), frames[1]], [frames[0], torch.from_numpy(frames[1]).cuda()]):
+        got = vg.generate_batch(batch, device_outputs=False)
+        rb = [oracle.generate(geom, np.ascontiguousarray(f.cpu().numpy() if hasattr(f, "cpu") else f), 900, 15) for f in batch]
+        assert got["voxel_num"].tolist() == [len(r[2]) for r in rb]
+        util.assert_vox_equal((got["voxels"], got["coordinates"], got["num_points_per_voxel"]),
+                              (np.concatenate([r[0] for r in rb]),
+                               np.concatenate([np.pad(r[1], ((0, 0), (0, 1)), constant_values=i) for i, r in enumerate(rb)]),
+                               np.concatenate([r[2] for r in rb])))
     vg.close()
 
 
