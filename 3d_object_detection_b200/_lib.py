@@ -102,7 +102,7 @@ def load():
     L.pf_stage_copy.restype = C.c_int
     L.pf_stage_copy.argtypes = [_p, _p, C.c_size_t, C.c_int]
     L.pf_frame_run.restype = C.c_int
-    L.pf_frame_run.argtypes = [C.c_int, _p, _p, _p, _p, _p, _p, C.c_size_t, C.c_int, _p, C.c_int, _p, C.POINTER(C.c_int32)]
+    L.pf_frame_run.argtypes = [C.c_int, _p, _p, _p, _p, _p, _p, C.c_size_t, C.c_int, _p, _p, C.c_int, _p, C.POINTER(C.c_int32)]
     L.pf_frame_copy_out.restype = C.c_int
     L.pf_frame_copy_out.argtypes = [C.c_int, _p, _p, C.c_size_t, _p, _p, C.c_size_t, _p, _p, C.c_size_t, _p, _p, C.c_int]
     L.pf_upload_frames.restype = C.c_int

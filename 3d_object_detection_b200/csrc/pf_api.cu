@@ -292,19 +292,33 @@ int pf_copy3(void *dst0, const void *src0, size_t bytes0, void *dst1, const void
 // Host side of one VoxelGenerator.generate call in ONE library call (the interpreter costs more than the copies here):
 // stage the frame, replay the frame graph, wait, read the voxel count.
 int pf_frame_run(int device, void *graph_exec, void *stream, void *done_event, void *pending_event, void *pinned_points,
-                 const void *points, size_t bytes, int threads, int32_t *pinned_offsets, int n_points,
+                 const void *points, size_t bytes, int threads, void *device_points, int32_t *pinned_offsets, int n_points,
                  const int32_t *pinned_voxel_num, int32_t *voxel_num)
 {
     if (!graph_exec || !done_event || !pinned_offsets || !pinned_voxel_num || !voxel_num || n_points < 0)
         return fail(PF_ERR_INVALID_ARGUMENT, "pf_frame_run: bad argument");
-    if (bytes > 0) {
-        if (int rc = pf_stage_copy(pinned_points, points, bytes, threads)) return rc;
-    }
+    if (bytes > 0 && (!pinned_points || !points)) return fail(PF_ERR_INVALID_ARGUMENT, "pf_frame_run: null points / staging buffer");
     pinned_offsets[0] = 0, pinned_offsets[1] = n_points;
     DeviceGuard guard(device);
     Range nvtx_range("pf_frame_run");
     cudaStream_t st = static_cast<cudaStream_t>(stream);
     cudaError_t e = cudaSuccess;
+    if (bytes > 0 && device_points) {
+        // the upload is not part of the graph: the frame is staged in up to four pieces and every piece goes to the copy
+        // engine as soon as it is staged, so all but the first staging copy (and the graph launch) run under the DMA
+        size_t chunk = (bytes + 3) / 4;
+        if (chunk < (1u << 20)) chunk = 1u << 20;
+        chunk = (chunk + 4095) & ~(size_t)4095;
+        for (size_t off = 0; off < bytes && e == cudaSuccess; off += chunk) {
+            const size_t len = bytes - off < chunk ? bytes - off : chunk;
+            if (int rc = pf_stage_copy(static_cast<char *>(pinned_points) + off, static_cast<const char *>(points) + off, len, threads)) return rc;
+            e = cudaMemcpyAsync(static_cast<char *>(device_points) + off, static_cast<const char *>(pinned_points) + off, len,
+                                cudaMemcpyHostToDevice, st);
+        }
+        if (e != cudaSuccess) return cuda_fail(e, "pf_frame_run: upload");
+    } else if (bytes > 0) {
+        if (int rc = pf_stage_copy(pinned_points, points, bytes, threads)) return rc;
+    }
     if (pending_event) e = cudaStreamWaitEvent(st, static_cast<cudaEvent_t>(pending_event), 0);
     if (e == cudaSuccess) e = cudaGraphLaunch(static_cast<cudaGraphExec_t>(graph_exec), st);
     if (e == cudaSuccess) e = cudaEventRecord(static_cast<cudaEvent_t>(done_event), st);

@@ -37,7 +37,8 @@ class FusedFramePath:
         self.graphs = {}                              # staged rows -> (CUDAGraph, cudaGraphExec_t)
 
     def _body(self, rows: int):
-        self.d_pts[:rows].copy_(self.h_pts[:rows], non_blocking=True)
+        if rows:                                      # rows == 0: pf_frame_run uploads the points in front of the graph
+            self.d_pts[:rows].copy_(self.h_pts[:rows], non_blocking=True)
         self.d_offs.copy_(self.h_offs, non_blocking=True)
         feats = self.fe.voxelize_pfn(self.d_pts, self.d_offs, self.folded, n_frames=1, max_frame_points=self.cap)
         self.fe.scatter(feats, n_frames=1)
@@ -59,15 +60,16 @@ class FusedFramePath:
         return g
 
     def run(self, points, n: int, threads: int):
-        from .voxel_generator import _raw_stream
+        from .voxel_generator import _CHUNKED_UPLOAD, _raw_stream
         src = points if points.flags.c_contiguous else points.copy()
-        rows = min(self.cap, max(4096, (n + 4095) // 4096 * 4096))
+        rows = 0 if _CHUNKED_UPLOAD else min(self.cap, max(4096, (n + 4095) // 4096 * 4096))
         _, exec_ptr = self._graph(rows)
         # stage, replay on the caller's current stream (ordered behind the consumer of the previous canvas, in front of the
         # consumer of this one), wait, read V: one foreign call
         idx = self.dev.index
         rc = self.fe.handle.lib.pf_frame_run(idx, exec_ptr, _raw_stream(idx), self.ev_done, None, self.p_stage,
-                                             src.ctypes.data if n else None, src.nbytes if n else 0, threads, self.p_offs, n,
+                                             src.ctypes.data if n else None, src.nbytes if n else 0, threads,
+                                             self.d_pts.data_ptr() if _CHUNKED_UPLOAD else None, self.p_offs, n,
                                              self.p_vnum, C.byref(self.c_v))
         if rc:
             _lib.check(rc, "pf_frame_run")

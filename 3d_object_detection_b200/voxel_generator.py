@@ -48,6 +48,11 @@ from . import _lib
 from .config import derive_grid
 
 _BUCKET = 32768          # point-capacity granularity of the single-frame graphs
+# PF_FRAME_UPLOAD=chunked: pf_frame_run uploads the points itself, piece by piece as they are staged, in front of a graph
+# without a points copy.  Measured and NOT the default (profiles/r2_frame_probe_upload.txt): the copy inside the graph wins
+# by 3-10 us (20 cm 138 vs 142 us, nuScenes 243 vs 252, 10 cm 218 vs 222): four extra cudaMemcpyAsync calls and a graph
+# launch behind them cost more than the staging time they hide.
+_CHUNKED_UPLOAD = os.environ.get("PF_FRAME_UPLOAD", "graph") == "chunked"
 _POOL_MAX = 8            # pinned output blocks kept per instance before falling back to pageable copies
 
 
@@ -118,6 +123,7 @@ class _FramePath:
             self.ev_done, self.ev_copy = self.event.cuda_event, self.copy_event.cuda_event
             self.p_stage, self.p_offs, self.p_vnum = self.h_pts.data_ptr(), self.h_offs.data_ptr(), self.h_vnum.data_ptr()
             self.p_voxels, self.p_coors, self.p_num = self.voxels.data_ptr(), self.coors.data_ptr(), self.num.data_ptr()
+            self.p_dpts = self.d_pts.data_ptr()
             self.c_v = C.c_int32(0)
             self.lib = self.handle.lib
 
@@ -125,7 +131,8 @@ class _FramePath:
         torch = _torch()
         h = self.handle
         if src_host:
-            self.d_pts[:rows].copy_(self.h_pts[:rows], non_blocking=True)
+            if rows:                                  # rows == 0: pf_frame_run uploads the points in front of the graph
+                self.d_pts[:rows].copy_(self.h_pts[:rows], non_blocking=True)
             self.d_offs.copy_(self.h_offs, non_blocking=True)
         stream = torch.cuda.current_stream(self.dev).cuda_stream
         _lib.check(h.lib.pf_voxelize(h.ptr, self.d_pts.data_ptr(), self.d_offs.data_ptr(), 1, self.cap, self.F, 0, 3,
@@ -134,7 +141,8 @@ class _FramePath:
         self.h_vnum.copy_(self.vnum, non_blocking=True)
 
     def graph_for(self, rows: int):
-        """The graph whose H2D node moves `rows` staged point rows (rows is a multiple of 4096 <= cap)."""
+        """The graph whose H2D node moves `rows` staged point rows (rows is a multiple of 4096 <= cap); rows == 0: the graph
+        without an upload of the points (offsets H2D, kernels, D2H of V), for the chunked upload of pf_frame_run."""
         torch = _torch()
         g = self.graphs.get(rows)
         if g is None:
@@ -293,15 +301,17 @@ class VoxelGenerator:
         torch = _torch()
         path = self._path(n_feat, n)
         src = points if points.flags.c_contiguous else np.ascontiguousarray(points)
-        rows = min(path.cap, max(4096, (n + 4095) // 4096 * 4096))      # rows the graph's H2D node moves
+        # the upload of the staged frame is a node of the graph (rows = what it moves); PF_FRAME_UPLOAD=chunked: see above
+        chunked = _CHUNKED_UPLOAD
+        rows = 0 if chunked else min(path.cap, max(4096, (n + 4095) // 4096 * 4096))
         _, exec_ptr = path.graph_for(rows)
         dev_idx = self._device_index
         raw = _raw_stream(dev_idx)                    # replay on the caller's current stream, like every other call
         lib = path.lib
         # a hand-out copy of the previous call may still be running, possibly on another stream: the replay waits for it
         rc = lib.pf_frame_run(dev_idx, exec_ptr, raw, path.ev_done, path.ev_copy if path.copy_pending else None, path.p_stage,
-                              src.ctypes.data if n else None, src.nbytes if n else 0, self._threads, path.p_offs, n, path.p_vnum,
-                              C.byref(path.c_v))
+                              src.ctypes.data if n else None, src.nbytes if n else 0, self._threads,
+                              path.p_dpts if chunked else None, path.p_offs, n, path.p_vnum, C.byref(path.c_v))
         if rc:
             _lib.check(rc, "pf_frame_run")
         path.copy_pending = False

@@ -100,15 +100,20 @@ PF_API int pf_copy3(void *dst0, const void *src0, size_t bytes0, void *dst1, con
 
 /* Host side of ONE single-frame call (VoxelGenerator.generate, framework/voxel_generator.py:28-40; the reference's operating
  * point is one frame per call) in one library call, so that the host language pays one foreign call instead of six:
- * copy `bytes` of `points` (pageable) into `pinned_points` with up to `threads` host threads, write the frame offsets
- * {0, n_points} into `pinned_offsets`, make `stream` wait for `pending_event` (may be NULL: a hand-out copy of the previous
- * call on another stream), launch `graph_exec` -- a cudaGraphExec_t the caller captured once: H2D of the staged frame and
+ * copy `bytes` of `points` (pageable) into `pinned_points` with up to `threads` host threads (streaming stores), write the
+ * frame offsets {0, n_points} into `pinned_offsets`, make `stream` wait for `pending_event` (may be NULL: a hand-out copy of
+ * the previous call on another stream), launch `graph_exec` -- a cudaGraphExec_t the caller captured once: H2D of the
  * offsets, pf_voxelize*, D2H of the voxel count into `pinned_voxel_num` -- on `stream`, record `done_event` (a cudaEvent_t
- * of the caller), wait for it and return the voxel count.  `device` is made current for the call.  This is the only call of
- * the library that synchronises, by design: the row count of the outputs is data dependent. */
+ * of the caller), wait for it and return the voxel count.
+ *   device_points != NULL: the upload of the points is done HERE, in front of the graph: the frame is staged in up to four
+ *                          pieces and each piece is handed to the copy engine as soon as it is staged (the graph then holds
+ *                          no copy of the points);
+ *   device_points == NULL: the whole frame is staged first and the graph is expected to contain the H2D of the staging buffer.
+ * `device` is made current for the call.  This is the only call of the library that synchronises, by design: the row count of
+ * the outputs is data dependent. */
 PF_API int pf_frame_run(int device, void *graph_exec, void *stream, void *done_event, void *pending_event,
-                        void *pinned_points, const void *points, size_t bytes, int threads, int32_t *pinned_offsets,
-                        int n_points, const int32_t *pinned_voxel_num, int32_t *voxel_num);
+                        void *pinned_points, const void *points, size_t bytes, int threads, void *device_points,
+                        int32_t *pinned_offsets, int n_points, const int32_t *pinned_voxel_num, int32_t *voxel_num);
 /* The hand-out that follows: pf_copy3, then `record_event` (may be NULL) recorded on `stream`, then, if `synchronize`, a wait
  * for the stream (pinned host destinations that are returned to the caller as numpy arrays). */
 PF_API int pf_frame_copy_out(int device, void *dst0, const void *src0, size_t bytes0, void *dst1, const void *src1,

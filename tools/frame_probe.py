@@ -61,11 +61,14 @@ import ctypes as C  # noqa: E402
 c_v = C.c_int32(0)
 raw = torch.cuda.current_stream(path.dev).cuda_stream
 side = path.stream.cuda_stream
+g0, g0_exec = path.graph_for(0)
+print(f"  pf_frame_run, chunked upload in front of the graph, {vg._threads} threads: "
+      f"{t(lambda: lib.pf_frame_run(path.dev.index, g0_exec, raw, path.ev_done, None, path.p_stage, frame.ctypes.data, frame.nbytes, vg._threads, path.p_dpts, path.p_offs, n, path.p_vnum, C.byref(c_v))):7.1f} us")
 for name, st in (("current (default) stream", raw), ("side stream", side)):
     for thr in (0, vg._threads):
         nb = frame.nbytes if thr else 0
         print(f"  pf_frame_run on the {name}, stage threads {thr}: "
-              f"{t(lambda: lib.pf_frame_run(path.dev.index, g_exec, st, path.ev_done, None, path.p_stage, frame.ctypes.data, nb, max(thr, 1), path.p_offs, n, path.p_vnum, C.byref(c_v))):7.1f} us")
+              f"{t(lambda: lib.pf_frame_run(path.dev.index, g_exec, st, path.ev_done, None, path.p_stage, frame.ctypes.data, nb, max(thr, 1), None, path.p_offs, n, path.p_vnum, C.byref(c_v))):7.1f} us")
 
 
 def replay_wait_default():
