@@ -387,7 +387,7 @@ int pf_debug_set_fill_variant(int variant)
 int pf_debug_set_pdl(int enable)
 {
     pf::set_pdl(enable);
-    return pf::pdl_enabled() ? 1 : 0;
+    return pf::pdl_state();
 }
 
 int pf_debug_stage_times(pf_handle *h, float *ms, int capacity)

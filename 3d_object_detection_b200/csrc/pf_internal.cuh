@@ -134,7 +134,8 @@ cudaError_t launch_anchor_mask(const int32_t *coors, int coors_stride, const int
 
 size_t gather_smem_needed(int P, int F);   // pf_voxelize.cu
 bool pdl_enabled();            // pf_voxelize.cu: launch the chain kernels as programmatic dependents (PF_PDL / pf_debug_set_pdl)
-void set_pdl(int on);
+void set_pdl(int on);     // 0 off, 1 on, < 0 auto
+int pdl_state();          // 0 off, 1 on, 2 auto
 bool pdl_stage(int bit);   // experiments: PF_PDL_MASK selects which launches are dependents
 
 #if defined(__CUDACC__)

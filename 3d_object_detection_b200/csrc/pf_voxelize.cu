@@ -216,25 +216,30 @@ static cudaError_t dispatch_gather(const Params &p, const Work &w, const GatherA
                 : run_gather<32, FROM_POINTS, false>(p, w, a, grid_g32, stream);
 }
 
-// Programmatic dependent launch of the chain kernels: OFF by default, PF_PDL=1 / pf_debug_set_pdl(1) turns it on.
+// Programmatic dependent launch of the chain kernels.  Modes: 0 = off (the default), 1 = on for the launches PF_PDL_MASK
+// selects (PF_PDL=1), 2 = "auto" (PF_PDL=2): only the second quantize range of a SINGLE-frame call is a dependent.
 // Measured (profiles/r2_chain_experiments.md E5): the second quantize range and the canvas fill as dependents save 4-5 us of a
 // serial step, the five kernels between them lose 7-10 us (the early-resident dependents take issue slots and shared memory
-// from their predecessor's tail), and with two or three front ends in flight every form of it is slower (0.290 -> 0.329 ms).
+// from their predecessor's tail), and with two or three front ends in flight every form of it is slower (0.290 -> 0.329 ms);
+// a lone frame (the drop-in path: one front end) gains 2-5 us from the quantize boundary and nothing more -- inside generate()
+// that is within the noise (call AN: 143.1 against 143.9 us), so even "auto" is not the default.
 static int g_pdl = -1;
 static int g_pdl_mask = 0x7f;   // experiments: which launches are dependents (bit 0 quantize range 2, 1 assign, 2 tile_rank,
                                 // 3 column_scan, 4 slot, 5 gather, 6 canvas fill); PF_PDL_MASK
-bool pdl_enabled()
+static int pdl_mode()
 {
     if (g_pdl < 0) {
         const char *e = getenv("PF_PDL");
-        g_pdl = (e && e[0] == '1') ? 1 : 0;
+        g_pdl = !e ? 0 : (e[0] == '1' ? 1 : (e[0] == '2' ? 2 : 0));
         const char *m = getenv("PF_PDL_MASK");
         if (m) g_pdl_mask = (int)strtol(m, nullptr, 0);
     }
-    return g_pdl != 0;
+    return g_pdl;
 }
+bool pdl_enabled() { return pdl_mode() == 1; }
 bool pdl_stage(int bit) { return pdl_enabled() && ((g_pdl_mask >> bit) & 1); }
-void set_pdl(int on) { g_pdl = on ? 1 : 0; }
+void set_pdl(int on) { g_pdl = on < 0 ? 2 : (on ? 1 : 0); }
+int pdl_state() { return pdl_mode(); }
 
 cudaError_t launch_voxelize(const Params &p, const Work &w, const VoxelizeArgs &a, cudaStream_t stream)
 {
@@ -253,14 +258,15 @@ cudaError_t launch_voxelize(const Params &p, const Work &w, const VoxelizeArgs &
     // its launch, index arithmetic and shared-memory clears run under the predecessor's tail.  Off while the stage events
     // are recorded (an event between two kernels is a full dependency anyway).
     const bool dep = pdl_enabled() && !w.ev;
+    const bool dep_q = !w.ev && (pdl_mode() == 2 ? B == 1 : pdl_stage(0));   // second quantize range behind the first
     cudaError_t le = cudaSuccess;
     mark(w, kEvStart, stream);
     for (int pass = 0; pass < 2; ++pass) {
         const int lo = pass == 0 ? 0 : split, hi = pass == 0 ? split : npts;
         if (lo >= hi) continue;
         const dim3 g((hi - lo + kPtsPerCta - 1) / kPtsPerCta, B);
-        if (vec4) le = launch_k(k_quantize<true>, g, dim3(256), 0, stream, dep && pass == 1 && pdl_stage(0), p, w, a.points, a.frame_offsets, a.point_stride, lo, hi);
-        else      le = launch_k(k_quantize<false>, g, dim3(256), 0, stream, dep && pass == 1 && pdl_stage(0), p, w, a.points, a.frame_offsets, a.point_stride, lo, hi);
+        if (vec4) le = launch_k(k_quantize<true>, g, dim3(256), 0, stream, dep_q && pass == 1, p, w, a.points, a.frame_offsets, a.point_stride, lo, hi);
+        else      le = launch_k(k_quantize<false>, g, dim3(256), 0, stream, dep_q && pass == 1, p, w, a.points, a.frame_offsets, a.point_stride, lo, hi);
         if (le != cudaSuccess) return le;
     }
     mark(w, kEvQuantize, stream);

@@ -166,12 +166,14 @@ PF_API int pf_debug_stage_timing(pf_handle *h, int enable);
  * variant now in force, or a negative pf_status. */
 PF_API int pf_debug_set_fill_variant(int variant);
 /* Diagnostics / A-B measurements: programmatic dependent launch of the chain (process-wide; also the environment variables
- * PF_PDL=1 and PF_PDL_MASK read at first use).  OFF by default.  When on, the kernels of pf_voxelize* after the first and the
- * canvas fill of pf_scatter_from_map are launched with the programmatic-stream-serialization attribute: they are scheduled
- * while the kernel in front of them on the stream drains, do their index arithmetic and shared-memory clears, and wait
- * (griddepcontrol.wait) before they read anything that kernel wrote.  Results are identical either way; graphs captured
- * while it is on keep the programmatic edges.  It is off because it measured slower whenever more than one front end is
- * in flight (profiles/r2_chain_experiments.md E5).  Returns the state now in force (0 / 1). */
+ * PF_PDL=0|1|2 and PF_PDL_MASK read at first use).  enable = 1: the kernels of pf_voxelize* after the first and the canvas fill
+ * of pf_scatter_from_map are launched with the programmatic-stream-serialization attribute: they are scheduled while the
+ * kernel in front of them on the stream drains, do their index arithmetic and shared-memory clears, and wait
+ * (griddepcontrol.wait) before they read anything that kernel wrote.  enable = 0: plain launches, the default.  enable < 0
+ * ("auto", PF_PDL=2): only the second quantize range of a single-frame call is a dependent.  Off by default because it measured
+ * slower whenever more than one front end is in flight and within the noise for a lone frame
+ * (profiles/r2_chain_experiments.md E5).  Results are identical in every mode; graphs captured while a mode is in force keep
+ * its edges.  Returns the state now in force (0 off, 1 on, 2 auto). */
 PF_API int pf_debug_set_pdl(int enable);
 PF_API int pf_debug_stage_times(pf_handle *h, float *ms, int capacity);
 

@@ -474,7 +474,8 @@ def test_pdl_switch_is_bit_identical(pf):
             got[on] = (graph, counts)
             fe.close()
     finally:
-        L.pf_debug_set_pdl(0)
+        assert L.pf_debug_set_pdl(-1) == 2          # "auto" is a state of its own ...
+        assert L.pf_debug_set_pdl(0) == 0           # ... and off is the default
     assert got[0][1].tolist() == got[1][1].tolist() and got[0][1][3] == 0
     mv = cfg["max_voxels"]
     for a, b in zip(got[0][0], got[1][0]):
